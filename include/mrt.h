@@ -1,0 +1,206 @@
+/*
+ * mrt.h — C-ABI of the B200 path-tracing core (libmrt_b200.so).
+ *
+ * The reference has no plugin/FFI interface; the boundary this library replaces is
+ *   (1) the Objective-C lifecycle of `Renderer` (reference: renderer/Renderer.h:5-6,
+ *       renderer/Renderer.mm:72-87, 255-470, 472-498, 500-585, 640-657), and
+ *   (2) the positional buffer bindings of its six GPU dispatches
+ *       (renderer/Renderer.mm:508-510, 519-523, 529-539, 545-553, 559-565, 577-579 <->
+ *       [[buffer(n)]] in renderer/Shaders.metal:75-79, 105-115, 214-221, 233-237).
+ * Every export below cites the reference interface it stands in for.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative
+ * MRT_E_* code, with a human-readable message available from mrt_last_error() (thread-local).
+ * A ctx owns all device memory and one in-order CUDA stream (the reference uses one
+ * MTLCommandQueue, Renderer.mm:153).  Host arrays passed in are borrowed for the duration of the
+ * call only.  A ctx is not thread-safe; distinct ctxs are independent.  There is NO CPU fallback:
+ * without a usable CUDA device mrt_create fails with MRT_E_CUDA.
+ */
+#ifndef MRT_H
+#define MRT_H
+
+#include "mrt_abi.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MRT_VERSION 100
+
+enum {
+    MRT_OK = 0,
+    MRT_E_INVALID = -1,   /* bad argument / call order */
+    MRT_E_CUDA = -2,      /* CUDA runtime error or no device */
+    MRT_E_NOMEM = -3,
+    MRT_E_IO = -4,        /* scene file problems */
+    MRT_E_STATE = -5      /* scene / size / noise not set yet */
+};
+
+/* Traversal / pipeline variant used by mrt_render_frames. */
+enum {
+    MRT_PIPELINE_AUTO = 0,
+    MRT_PIPELINE_MEGAKERNEL = 1,   /* one persistent fused kernel, ray state in registers */
+    MRT_PIPELINE_WAVEFRONT = 2     /* staged kernels with warp-ballot compaction of live rays */
+};
+
+/* How mrt_accumulate / mrt_render_frames fold a frame into the image. */
+enum {
+    MRT_ACCUM_MEAN = 0,   /* reference behaviour: c = mix(c, stored, f/(f+1)), Shaders.metal:241-247 */
+    MRT_ACCUM_SUM = 1,    /* image += radiance (sample-sharded multi-GPU; reduce, then mrt_scale_image) */
+    MRT_ACCUM_REPLACE = 2 /* ACCUMULATE_IMAGE == false, Raytracing.h:14 */
+};
+
+/* Device buffers reachable through the test seam (mrt_read_buffer / mrt_write_buffer). */
+enum {
+    MRT_BUF_RAYS = 0,            /* mrt_ray[W*H]                 Renderer.mm:651 */
+    MRT_BUF_LIGHT_RAYS = 1,      /* mrt_light_sampling_ray[W*H]  Renderer.mm:652 */
+    MRT_BUF_INTERSECTIONS = 2,   /* mrt_intersection[W*H]        Renderer.mm:653 */
+    MRT_BUF_IMAGE = 3            /* float4[W*H], row 0 = bottom  Renderer.mm:645-648 */
+};
+
+typedef struct mrt_ctx mrt_ctx;
+typedef struct mrt_scene mrt_scene;
+
+/* Compile-time macros of the reference (Raytracing.h:11-25) turned into run-time configuration.
+ * mrt_config_default() fills in the reference's values. */
+typedef struct mrt_config {
+    uint32_t struct_size;       /* = sizeof(mrt_config); checked */
+    int32_t  device;            /* CUDA device ordinal */
+    uint32_t max_path_length;   /* MAX_PATH_LENGTH, Raytracing.h:23 (1..64) */
+    uint32_t accumulate_mode;   /* MRT_ACCUM_*; default MEAN (ACCUMULATE_IMAGE true) */
+    uint32_t animate_noise;     /* ANIMATE_NOISE, Raytracing.h:20: frame f refreshes slot f%3 */
+    uint32_t pipeline;          /* MRT_PIPELINE_* */
+    uint32_t bvh_max_leaf;      /* SAH builder: max triangles per leaf (default 4) */
+    uint32_t bvh_threads;       /* SAH builder host threads (0 = hardware concurrency) */
+    uint32_t count_rays;        /* 1: maintain live-ray counters (mrt_stats) */
+    uint32_t reserved[7];
+} mrt_config;
+
+typedef struct mrt_stats {
+    uint64_t primary_rays;      /* live path segments traversed (maxDistance >= 0 at intersect time) */
+    uint64_t shadow_rays;       /* live light-sampling rays traversed */
+    uint64_t kernel_launches;   /* kernels of this library launched since mrt_create */
+    uint64_t frames_rendered;
+    uint64_t nodes_visited;     /* filled only by mrt_profile_traversal */
+    uint64_t triangles_tested;  /* filled only by mrt_profile_traversal */
+    float    last_render_ms;    /* device time of the last mrt_render_frames (CUDA events) */
+    uint32_t bvh_nodes;
+    uint32_t bvh_depth;
+    float    bvh_sah_cost;
+    float    bvh_build_ms;      /* host wall time of the last SAH build */
+    uint32_t reserved[5];
+} mrt_stats;
+
+/* Read-only view of a host scene container (arrays in the ABI layouts of mrt_abi.h). */
+typedef struct mrt_scene_view {
+    const mrt_vertex* vertices;               uint32_t vertex_count;
+    const uint32_t* indices;                  uint32_t triangle_count;   /* 3 per triangle */
+    const mrt_triangle_reference* references;                          /* triangle_count */
+    const mrt_material* materials;            uint32_t material_count;
+    const mrt_light_triangle* lights;         uint32_t light_count;      /* array has light_count+1 */
+} mrt_scene_view;
+
+/* ---- errors / version ------------------------------------------------------------------- */
+const char* mrt_last_error(void);
+int  mrt_version(void);
+void mrt_config_default(mrt_config* cfg);
+
+/* ---- lifecycle -------------------------------------------------------------------------- */
+/* -[Renderer initWithMetalKitView:] + loadMetalWithView: (Renderer.mm:72-154): device, queue,
+ * per-frame SharedData and the three noise slots (zero-filled until mrt_set_noise). */
+int mrt_create(const mrt_config* cfg, mrt_ctx** out);
+int mrt_destroy(mrt_ctx* ctx);
+
+/* Buffer upload + acceleration structure of -initRaytracing (Renderer.mm:450-469): vertex
+ * (stride 24) / uint32 index / TriangleReference / Material / LightTriangle buffers, then a SAH BVH
+ * built on the host replaces MPSTriangleAccelerationStructure -rebuild.  `lights` holds
+ * light_count+1 entries (sentinel last, Renderer.mm:444-448). */
+int mrt_set_scene(mrt_ctx* ctx,
+                  const mrt_vertex* vertices, uint32_t vertex_count,
+                  const uint32_t* indices, uint32_t triangle_count,
+                  const mrt_triangle_reference* references,
+                  const mrt_material* materials, uint32_t material_count,
+                  const mrt_light_triangle* lights, uint32_t light_count);
+int mrt_set_scene_from(mrt_ctx* ctx, const mrt_scene* scene);
+
+/* -mtkView:drawableSizeWillChange: (Renderer.mm:640-657): (re)allocate Ray / LightSamplingRay /
+ * Intersection / image for width x height rays, zero-fill, restart accumulation.  width/height are
+ * the DISPATCH size (the reference's CONTENT_SCALE x drawable size). */
+int mrt_resize(mrt_ctx* ctx, uint32_t width, uint32_t height);
+
+/* Noise slot upload (Renderer.mm:115-129 initial fill, 492-496 per-frame refresh).
+ * slot in [0,3); tile = 64*64 float4 in [0,1). */
+int mrt_set_noise(mrt_ctx* ctx, uint32_t slot, const float* tile);
+
+/* Multi-GPU row sharding: this ctx renders only rows y with y % row_stride == first_row.
+ * (0,1) = whole image.  No reference counterpart (single device). */
+int mrt_set_row_shard(mrt_ctx* ctx, uint32_t first_row, uint32_t row_stride);
+int mrt_set_accumulate_mode(mrt_ctx* ctx, uint32_t mode);
+int mrt_set_pipeline(mrt_ctx* ctx, uint32_t pipeline);
+
+/* ---- the six dispatch kinds, one entry point each (asynchronous on the ctx stream) ---------- */
+/* rayGenerator, Shaders.metal:75-103; bindings Renderer.mm:508-510 (noise slot frame%3). */
+int mrt_raygen(mrt_ctx* ctx, uint32_t frame_index);
+/* MPSRayIntersector nearest hit, Renderer.mm:519-523 (which = MRT_BUF_RAYS, stride 80) and
+ * 545-553 (which = MRT_BUF_LIGHT_RAYS, stride 48); writes the single shared Intersection buffer.
+ * Semantics of Renderer.mm:464-469: no culling, no masks, rays with maxDistance < 0 are skipped and
+ * report distance < 0. */
+int mrt_intersect(mrt_ctx* ctx, uint32_t which);
+/* intersectionHandler, Shaders.metal:105-212; bindings Renderer.mm:529-539
+ * (noise slot (frame+bounce_iteration)%3). */
+int mrt_shade(mrt_ctx* ctx, uint32_t frame_index, uint32_t bounce_iteration);
+/* lightSamplingHandler, Shaders.metal:214-231; bindings Renderer.mm:559-565. */
+int mrt_shadow_resolve(mrt_ctx* ctx);
+/* accumulateImage, Shaders.metal:233-249; bindings Renderer.mm:577-579. */
+int mrt_accumulate(mrt_ctx* ctx, uint32_t frame_index);
+
+/* -performRaytracing: (Renderer.mm:500-585) as the reference sequences it: raygen, then
+ * max_path_length x {intersect, shade, intersect, resolve}, then accumulate — 2 + 4*L launches
+ * through the full-size stage buffers.  Does not touch the noise slots. */
+int mrt_render_frame_staged(mrt_ctx* ctx, uint32_t frame_index);
+
+/* The production path: frames first_frame, first_frame+frame_stride, ... (n_frames of them)
+ * rendered by the fused sm_100a pipeline, bit-identical to the staged sequence.
+ * noise_tiles: host array of (n_frames-1)*frame_stride+1 tiles, tile k belongs to frame
+ * first_frame+k and refreshes slot (first_frame+k)%3 before that frame is rendered, exactly as
+ * -updateSharedData does (Renderer.mm:485-497).  NULL = no refresh (ANIMATE_NOISE 0).  On return
+ * the three slots hold what the reference's would after the last frame.  Asynchronous. */
+int mrt_render_frames(mrt_ctx* ctx, uint32_t first_frame, uint32_t n_frames, uint32_t frame_stride,
+                      const float* noise_tiles);
+int mrt_sync(mrt_ctx* ctx);
+
+/* ---- results / test seams ------------------------------------------------------------------- */
+/* Image read-back (the reference never reads back; -saveCurrentImage is a stub, Renderer.mm:659-662).
+ * rgba: width*height*4 floats, row 0 = bottom row. */
+int mrt_read_image(mrt_ctx* ctx, float* rgba);
+int mrt_scale_image(mrt_ctx* ctx, float scale);          /* rgb *= scale, alpha = 1 */
+int mrt_clear_image(mrt_ctx* ctx);
+int mrt_image_device_ptr(mrt_ctx* ctx, void** device_ptr, size_t* bytes); /* for NCCL reduce */
+int mrt_read_buffer(mrt_ctx* ctx, uint32_t which, void* dst, size_t bytes);
+int mrt_write_buffer(mrt_ctx* ctx, uint32_t which, const void* src, size_t bytes);
+int mrt_get_stats(mrt_ctx* ctx, mrt_stats* out);
+int mrt_reset_stats(mrt_ctx* ctx);
+
+/* Stand-alone replacement of one MPSRayIntersector encode (Renderer.mm:464-469, 519-523): `rays`
+ * is a HOST array of `count` records of `stride_bytes` each whose first 32 bytes are
+ * origin[3], minDistance, direction[3], maxDistance; `out` receives count intersections. */
+int mrt_intersect_host(mrt_ctx* ctx, const void* rays, size_t stride_bytes, uint32_t count,
+                       mrt_intersection* out);
+/* Same rays through an instrumented traversal; adds node/triangle visit counts to mrt_stats. */
+int mrt_profile_traversal(mrt_ctx* ctx, const void* rays, size_t stride_bytes, uint32_t count);
+
+/* ---- caller-side helpers (host only; usable without a GPU) ---------------------------------- */
+/* Scene -> ABI buffers, the job of -initRaytracing before upload (Renderer.mm:257-448):
+ * materials, triangle references, light list with pdf/cdf and sentinel. */
+int  mrt_scene_create_procedural(const char* name, uint64_t seed, mrt_scene** out);
+int  mrt_scene_load_obj(const char* obj_path, mrt_scene** out);
+int  mrt_scene_get(const mrt_scene* scene, mrt_scene_view* view);
+void mrt_scene_destroy(mrt_scene* scene);
+/* Noise tile for (seed, frame): 64*64*4 floats, (mt19937_64(seed ^ frame)() >> 40) * 2^-24.
+ * Stands in for the clock-seeded fills of Renderer.mm:109-126, 486-495. */
+void mrt_noise_fill(uint64_t seed, uint32_t frame, float* tile);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MRT_H */

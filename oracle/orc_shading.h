@@ -1,0 +1,200 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_abi.h).
+//
+// orc_shading.h — scalar C++ restatement of the reference's device helpers:
+//   renderer/KernelHelpers.h:7-190, the device half of renderer/Raytracing.h:168-223, and
+//   renderer/Spectrum.h:25-113.  One function per reference function, same names, each citing the
+//   lines it follows.  Quirks are kept verbatim (see SURVEY.md §3.3 "Edge behaviours").
+#pragma once
+#include "orc_abi.h"
+#include "orc_math.h"
+
+namespace orc {
+
+struct Vtx { f3 v, n; };                               // thread-space Vertex
+static inline Vtx load_vertex(const Vertex& p) { return Vtx{ld3(p.v), ld3(p.n)}; }
+
+// ---- Spectrum.h:25-113 -----------------------------------------------------------------------
+static inline void spectrum_set(Spectrum& a, float value) {                      // :25-31
+    for (int i = 0; i < SPECTRUM_SAMPLES; ++i) a.values[i] = value;
+}
+static inline void spectrum_add_inplace(Spectrum& a, const Spectrum& b) {        // :33-47
+    for (int i = 0; i < SPECTRUM_SAMPLES; ++i) a.values[i] += b.values[i];
+}
+static inline void spectrum_mul_inplace(Spectrum& a, const Spectrum& b) {        // :49-63
+    for (int i = 0; i < SPECTRUM_SAMPLES; ++i) a.values[i] *= b.values[i];
+}
+static inline void spectrum_mul_inplace(Spectrum& a, float b) {                  // :65-71
+    for (int i = 0; i < SPECTRUM_SAMPLES; ++i) a.values[i] *= b;
+}
+static inline Spectrum spectrum_mul(const Spectrum& a, float b) {                // :79-89
+    Spectrum r; for (int i = 0; i < SPECTRUM_SAMPLES; ++i) r.values[i] = a.values[i] * b; return r;
+}
+static inline Spectrum spectrum_mul(const Spectrum& a, const Spectrum& b) {      // :91-113
+    Spectrum r; for (int i = 0; i < SPECTRUM_SAMPLES; ++i) r.values[i] = a.values[i] * b.values[i]; return r;
+}
+
+// ---- Raytracing.h:168-223 ----------------------------------------------------------------------
+static inline float triangleSamplePDF(float area, float cosTheta, float distanceToSample) {  // :168-171
+    return (distanceToSample * distanceToSample) / (area * cosTheta);
+}
+static inline float balanceHeuristic(float fPdf, float gPdf) {                   // :173-178 (power-2)
+    float f2 = fPdf * fPdf;
+    float g2 = gPdf * gPdf;
+    return f2 / (f2 + g2);
+}
+static inline f3 barycentric(f2 smp) {                                           // :182-187
+    float r1 = std::sqrt(smp.x);
+    float r2 = smp.y;
+    return f3{1.0f - r1, r1 * (1.0f - r2), r1 * r2};
+}
+static inline void buildOrthonormalBasis(f3 n, f3& u, f3& v) {                   // :189-205
+    if (n.z < 0.0f) {
+        float a = 1.0f / (1.0f - n.z);
+        float b = n.x * n.y * a;
+        u = f3{1.0f - n.x * n.x * a, -b, n.x};
+        v = f3{b, n.y * n.y * a - 1.0f, -n.y};
+    } else {
+        float a = 1.0f / (1.0f + n.z);
+        float b = -n.x * n.y * a;
+        u = f3{1.0f - n.x * n.x * a, b, -n.x};
+        v = f3{b, 1.0f - n.y * n.y * a, -n.y};
+    }
+}
+static inline f3 alignWithNormal(f3 n, float cosTheta, float phi) {              // :207-216
+    float sinTheta = std::sqrt(1.0f - cosTheta * cosTheta);
+    f3 u, v;
+    buildOrthonormalBasis(n, u, v);
+    float s, c;
+    sincos_pinned(phi, &s, &c);
+    return (u * c + v * s) * sinTheta + n * cosTheta;
+}
+static inline f3 generateDiffuseBounce(f2 smp, f3 n) {                           // :218-223
+    float cosTheta = std::sqrt(smp.y);
+    float phi = smp.x * PI * 2.0f;
+    return alignWithNormal(n, cosTheta, phi);
+}
+
+// ---- KernelHelpers.h ---------------------------------------------------------------------------
+static inline float fresnel(f3 n, f3 i, float etaOut, float etaIn) {             // :7-21
+    float result = 1.0f;
+    float etaScale = etaOut / etaIn;
+    float cosThetaI = clampf(dot(n, i), -1.0f, 1.0f);
+    float sinThetaTSquared = (etaScale * etaScale) * (1.0f - cosThetaI * cosThetaI);
+    if (sinThetaTSquared < 1.0f) {
+        float cosThetaT = std::sqrt(1.0f - sinThetaTSquared);
+        float rS = (etaIn * cosThetaI - etaOut * cosThetaT) / (etaIn * cosThetaI + etaOut * cosThetaT);
+        float rP = (etaIn * cosThetaT - etaOut * cosThetaI) / (etaIn * cosThetaT + etaOut * cosThetaI);
+        result = 0.5f * (rS * rS + rP * rP);
+    }
+    return result;
+}
+
+static inline Vtx interpolate(const Vtx& t0, const Vtx& t1, const Vtx& t2, f3 uvw) {   // :23-37
+    Vtx r;
+    r.v = madd(t2.v, uvw.z, madd(t1.v, uvw.y, t0.v * uvw.x));
+    r.n = normalize(madd(t2.n, uvw.z, madd(t1.n, uvw.y, t0.n * uvw.x)));
+    return r;
+}
+static inline Vtx interpolate(const Vtx& t0, const Vtx& t1, const Vtx& t2, f2 uv) {    // :39-47
+    return interpolate(t0, t1, t2, f3{uv.x, uv.y, 1.0f - uv.x - uv.y});
+}
+
+// :49-54 — linear scan of the exclusive CDF; may return the zero-area sentinel when xi >= sum(pdf)
+static inline const LightTriangle& selectLightTriangle(float xi, const LightTriangle* lightTriangles,
+                                                       int trianglesCount) {
+    int index = 0;
+    for (; (index < trianglesCount) && (lightTriangles[index + 1].cdf <= xi); ++index) {}
+    return lightTriangles[index];
+}
+
+static inline f2 mirrorLobe(f3 wI, f3 wO, f3 n, float cosTheta) {   // the expression repeated at :67-68, 83-84, 100-101
+    bool isMirrorDirection = std::fabs(dot(reflect(wI, n), wO) - 1.0f) < ANGLE_EPSILON;
+    return isMirrorDirection ? f2{cosTheta, 1.0f} : f2{0.0f, 1.0f};
+}
+
+// :56-114 — (bsdf*cos, pdf) of the material toward wO
+static inline f2 sampleMaterial(const Material& material, f3 wI, f3 wO, f3 n, f4 noiseSample) {
+    f2 result;
+    float cosTheta = dot(wO, n);            // un-clamped: may be negative (:61)
+    switch (material.materialType) {
+        case MATERIAL_MIRROR:
+            result = mirrorLobe(wI, wO, n, cosTheta);
+            break;
+        case MATERIAL_SMOOTH_PLASTIC: {
+            float fI = fresnel(n, -wI, 1.0f, material.ior);
+            if (fI < noiseSample.y) { float d = INV_PI * cosTheta; result = f2{d, d}; }
+            else result = mirrorLobe(wI, wO, n, cosTheta);
+            break;
+        }
+        case MATERIAL_SMOOTH_DIELECTRIC: {
+            float fI = fresnel(n, -wI, 1.0f, material.ior);
+            if (fI < noiseSample.y) result = f2{0.0f, 0.0f};     // "transmittance" (:95)
+            else result = mirrorLobe(wI, wO, n, cosTheta);
+            break;
+        }
+        default: {                                               // MATERIAL_DIFFUSE
+            float d = INV_PI * cosTheta; result = f2{d, d};
+            break;
+        }
+    }
+    return result;
+}
+
+// :116-179 — next direction and (bsdf, pdf, ior).  rayDirection / rayIor are rI.direction / rI.params.w.
+static inline f3 generateNextBounce(const Material& material, f3 rayDirection, float rayIor, f3 n,
+                                    f4 noiseSample, float& bsdf, float& pdf, float& ior) {
+    f3 wI = rayDirection;
+    f3 wO;
+    f2 properties;
+    float currentIoR = rayIor;
+    ior = currentIoR;
+    switch (material.materialType) {
+        case MATERIAL_MIRROR:
+            wO = reflect(wI, n);
+            properties = f2{dot(wO, n), 1.0f};
+            break;
+        case MATERIAL_SMOOTH_PLASTIC: {
+            float fI = fresnel(n, -wI, currentIoR, material.ior);
+            if (fI < noiseSample.y) {
+                wO = generateDiffuseBounce(f2{noiseSample.z, noiseSample.w}, n);
+                float d = INV_PI * dot(wO, n); properties = f2{d, d};
+            } else {
+                wO = reflect(wI, n);
+                properties = f2{dot(wO, n), 1.0f};
+            }
+            break;
+        }
+        case MATERIAL_SMOOTH_DIELECTRIC: {
+            float fI = fresnel(n, -wI, currentIoR, material.ior);
+            if (fI < noiseSample.y) {
+                ior = material.ior;
+                wO = wI;                                 // straight through, no refraction (:157)
+                properties = f2{1.0f, 1.0f};
+            } else {
+                wO = reflect(wI, n);
+                properties = f2{dot(wO, n), 1.0f};
+            }
+            break;
+        }
+        default: {                                       // MATERIAL_DIFFUSE
+            wO = generateDiffuseBounce(f2{noiseSample.z, noiseSample.w}, n);
+            float d = INV_PI * dot(wO, n); properties = f2{d, d};
+        }
+    }
+    bsdf = properties.x;
+    pdf = properties.y;
+    return wO;
+}
+
+// :181-190 — solid-angle pdf of a point on a light triangle, with validity mask; outputs unit direction
+static inline float lightTriangleSamplePDF(float trianglePdf, float triangleArea, f3 source, const Vtx& sample,
+                                           f3& directionToLight) {
+    directionToLight = sample.v - source;
+    float distanceToLight = length(directionToLight);
+    directionToLight = normalize(directionToLight);
+    float LdotD = -dot(directionToLight, sample.n);
+    float validDirection = float(distanceToLight >= DISTANCE_EPSILON) * float(LdotD >= ANGLE_EPSILON);
+    return validDirection * trianglePdf * triangleSamplePDF(triangleArea, LdotD, distanceToLight);
+}
+
+}  // namespace orc
