@@ -10,6 +10,13 @@
 using std::pow;
 #include "Raytracing.h"
 
+// JSON-safe float: Python's json reads NaN / Infinity / -Infinity
+static const char* J(double v) {
+    static char buf[16][40]; static int k = 0; char* b = buf[k++ & 15];
+    if (v != v) snprintf(b, 40, "NaN"); else if (v > 1e300) snprintf(b, 40, "Infinity"); else if (v < -1e300) snprintf(b, 40, "-Infinity");
+    else snprintf(b, 40, "%.9g", v);
+    return b;
+}
 #define SZ(T) printf("    \"%s\": {\"size\": %zu, \"align\": %zu", #T, sizeof(T), alignof(T))
 #define OFF(T, m) printf(", \"%s\": %zu", #m, offsetof(T, m))
 #define END() printf("}")
@@ -44,11 +51,11 @@ int main(int argc, char** argv) {
     printf("{\n  \"source\": \"renderer/Raytracing.h host functions run from the reference header\",\n");
     printf("  \"balanceHeuristic\": [");
     for (int i = 0; i < nx; ++i) for (int j = 0; j < nx; ++j)
-        printf("%s[%.9g, %.9g, %.9g]", (i || j) ? ", " : "", xs[i], xs[j], (double)balanceHeuristic(xs[i], xs[j]));
+        printf("%s[%.9g, %.9g, %s]", (i || j) ? ", " : "", xs[i], xs[j], J(balanceHeuristic(xs[i], xs[j])));
     printf("],\n  \"triangleSamplePDF\": [");
     for (int i = 1; i < nx; ++i) for (int j = 1; j < nx; ++j)
-        printf("%s[%.9g, %.9g, %.9g, %.9g]", (i > 1 || j > 1) ? ", " : "", xs[i], xs[j], xs[(i + j) % nx],
-               (double)triangleSamplePDF(xs[i], xs[j], xs[(i + j) % nx]));
+        printf("%s[%.9g, %.9g, %.9g, %s]", (i > 1 || j > 1) ? ", " : "", xs[i], xs[j], xs[(i + j) % nx],
+               J(triangleSamplePDF(xs[i], xs[j], xs[(i + j) % nx])));
     printf("],\n  \"toSRGB\": [");
     for (int i = 0; i < nx; ++i) printf("%s[%.9g, %.9g]", i ? ", " : "", xs[i], (double)toSRGB(xs[i]));
     printf("],\n  \"toLinear\": [");
