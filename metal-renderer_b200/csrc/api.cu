@@ -1,0 +1,528 @@
+// api.cu — the C-ABI of include/mrt.h: context, device memory, scene upload, stage entry points, fused render.
+//
+// Host-side counterpart of the reference's Renderer object (renderer/Renderer.mm): loadMetalWithView (:89-154),
+// initRaytracing (:255-470), updateSharedData (:472-498), performRaytracing (:500-585),
+// drawableSizeWillChange (:640-657).  No CPU fallback: every entry point that computes needs the CUDA device.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+#include "bvh.h"
+#include "kernels.h"
+#include "mrt.h"
+#include "scene.h"
+
+using namespace mrt;
+
+static thread_local std::string g_last_error;
+static int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    return fail(MRT_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+#define NEED(cond, code, ...) do { if (!(cond)) return fail(code, __VA_ARGS__); } while (0)
+
+#define MRT_STACK_DEPTH_HOST 62   /* traversal stack in device_trace.cuh holds 64 entries */
+static const size_t kTileFloat4 = MRT_NOISE_DIMENSIONS * MRT_NOISE_DIMENSIONS;
+static const size_t kTileBytes = kTileFloat4 * sizeof(float4);
+
+struct mrt_ctx {
+    mrt_config cfg{};
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, tableCopied = nullptr;
+    bool timed = false;
+    // scene
+    DeviceScene S{};
+    void* dNodes = nullptr; void* dTris = nullptr; void* dShade = nullptr; void* dMats = nullptr; void* dLights = nullptr;
+    void* dCdf = nullptr;
+    bool haveScene = false;
+    // per-size buffers (Renderer.mm:645-653)
+    uint32_t W = 0, H = 0, rowFirst = 0, rowStride = 1;
+    mrt_ray* dRays = nullptr; mrt_light_sampling_ray* dLightRays = nullptr; mrt_intersection* dIsects = nullptr;
+    float4* dImage = nullptr;
+    // noise: pool tiles 0..2 are the three slots; tiles 3.. hold a fused batch
+    float4* dNoisePool = nullptr; size_t poolTiles = 0;
+    uint4* dFrameTable = nullptr; FrameEntry* hFrameTable = nullptr; size_t tableCap = 0;
+    unsigned long long* dCounters = nullptr;     // primary, shadow, nodes, tris
+    mrt_stats stats{};
+
+    Grid2D grid() const { Grid2D g; g.W = W; g.H = H; g.rowFirst = rowFirst; g.rowStride = rowStride; return g; }
+    uint32_t ownedRows() const { return rowFirst < H ? (H - rowFirst + rowStride - 1) / rowStride : 0; }
+};
+
+static void free_scene(mrt_ctx* c) {
+    cudaFree(c->dNodes); cudaFree(c->dTris); cudaFree(c->dShade); cudaFree(c->dMats); cudaFree(c->dLights); cudaFree(c->dCdf);
+    c->dNodes = c->dTris = c->dShade = c->dMats = c->dLights = c->dCdf = nullptr;
+    c->haveScene = false;
+}
+static void free_sized(mrt_ctx* c) {
+    cudaFree(c->dRays); cudaFree(c->dLightRays); cudaFree(c->dIsects); cudaFree(c->dImage);
+    c->dRays = nullptr; c->dLightRays = nullptr; c->dIsects = nullptr; c->dImage = nullptr;
+}
+static int ensure_pool(mrt_ctx* c, size_t tiles) {
+    if (tiles <= c->poolTiles) return MRT_OK;
+    float4* p = nullptr;
+    CK(cudaMalloc(&p, tiles * kTileBytes));
+    if (c->dNoisePool) {
+        CK(cudaMemcpyAsync(p, c->dNoisePool, MRT_NOISE_SLOTS * kTileBytes, cudaMemcpyDeviceToDevice, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        cudaFree(c->dNoisePool);
+    } else {
+        CK(cudaMemsetAsync(p, 0, MRT_NOISE_SLOTS * kTileBytes, c->stream));
+    }
+    c->dNoisePool = p; c->poolTiles = tiles;
+    return MRT_OK;
+}
+static int ensure_table(mrt_ctx* c, size_t entries) {
+    if (entries <= c->tableCap) return MRT_OK;
+    CK(cudaStreamSynchronize(c->stream));
+    if (c->dFrameTable) cudaFree(c->dFrameTable);
+    if (c->hFrameTable) cudaFreeHost(c->hFrameTable);
+    c->dFrameTable = nullptr; c->hFrameTable = nullptr; c->tableCap = 0;
+    CK(cudaMalloc(&c->dFrameTable, entries * sizeof(uint4)));
+    CK(cudaMallocHost(&c->hFrameTable, entries * sizeof(FrameEntry)));
+    c->tableCap = entries;
+    return MRT_OK;
+}
+
+extern "C" {
+
+const char* mrt_last_error(void) { return g_last_error.c_str(); }
+int mrt_version(void) { return MRT_VERSION; }
+
+void mrt_config_default(mrt_config* cfg) {
+    if (!cfg) return;
+    std::memset(cfg, 0, sizeof *cfg);
+    cfg->struct_size = sizeof(mrt_config);
+    cfg->device = 0;
+    cfg->max_path_length = MRT_MAX_PATH_LENGTH;      // Raytracing.h:23
+    cfg->accumulate_mode = MRT_ACCUM_MEAN;           // ACCUMULATE_IMAGE true, Raytracing.h:14
+    cfg->animate_noise = 1;                          // Raytracing.h:20
+    cfg->pipeline = MRT_PIPELINE_AUTO;
+    cfg->bvh_max_leaf = 4;
+    cfg->bvh_threads = 0;
+    cfg->count_rays = 1;
+}
+
+int mrt_create(const mrt_config* cfg, mrt_ctx** out) {
+    NEED(out, MRT_E_INVALID, "mrt_create: out is NULL");
+    *out = nullptr;
+    mrt_config def; mrt_config_default(&def);
+    if (cfg) { NEED(cfg->struct_size == sizeof(mrt_config), MRT_E_INVALID, "mrt_create: struct_size %u != %zu", cfg->struct_size, sizeof(mrt_config)); def = *cfg; }
+    NEED(def.max_path_length >= 1 && def.max_path_length <= 64, MRT_E_INVALID, "max_path_length must be in 1..64");
+    NEED(def.accumulate_mode <= MRT_ACCUM_REPLACE, MRT_E_INVALID, "bad accumulate_mode");
+    NEED(def.pipeline <= MRT_PIPELINE_WAVEFRONT, MRT_E_INVALID, "bad pipeline");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) return fail(MRT_E_CUDA, "no CUDA device (%s); this library has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "count 0");
+    NEED(def.device >= 0 && def.device < n, MRT_E_INVALID, "device %d out of range (0..%d)", def.device, n - 1);
+    CK(cudaSetDevice(def.device));
+    mrt_ctx* c = new (std::nothrow) mrt_ctx();
+    NEED(c, MRT_E_NOMEM, "out of host memory");
+    c->cfg = def;
+    if (c->cfg.bvh_max_leaf == 0) c->cfg.bvh_max_leaf = 4;
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&c->ev0)); CK(cudaEventCreate(&c->ev1));
+    CK(cudaEventCreateWithFlags(&c->tableCopied, cudaEventDisableTiming));
+    CK(cudaMalloc(&c->dCounters, 4 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(c->dCounters, 0, 4 * sizeof(unsigned long long), c->stream));
+    int rc = ensure_pool(c, MRT_NOISE_SLOTS + 16);
+    if (rc) { delete c; return rc; }
+    *out = c;
+    return MRT_OK;
+}
+
+int mrt_destroy(mrt_ctx* c) {
+    if (!c) return MRT_OK;
+    cudaSetDevice(c->cfg.device);
+    cudaStreamSynchronize(c->stream);
+    free_scene(c); free_sized(c);
+    cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters);
+    if (c->hFrameTable) cudaFreeHost(c->hFrameTable);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->tableCopied);
+    cudaStreamDestroy(c->stream);
+    delete c;
+    return MRT_OK;
+}
+
+int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count, const uint32_t* indices, uint32_t triangle_count,
+                  const mrt_triangle_reference* references, const mrt_material* materials, uint32_t material_count,
+                  const mrt_light_triangle* lights, uint32_t light_count) {
+    NEED(c, MRT_E_INVALID, "ctx is NULL");
+    NEED(vertices && indices && references && materials && lights, MRT_E_INVALID, "mrt_set_scene: NULL array");
+    NEED(triangle_count < (1u << 28), MRT_E_INVALID, "triangle_count must be < 2^28");
+    for (size_t i = 0; i < 3 * (size_t)triangle_count; ++i)
+        NEED(indices[i] < vertex_count, MRT_E_INVALID, "index %zu = %u out of range (vertex_count %u)", i, indices[i], vertex_count);
+    for (uint32_t t = 0; t < triangle_count; ++t) {
+        const mrt_triangle_reference& r = references[t];
+        NEED(r.tri[0] < vertex_count && r.tri[1] < vertex_count && r.tri[2] < vertex_count, MRT_E_INVALID, "reference %u: vertex index out of range", t);
+        NEED(r.materialIndex < material_count, MRT_E_INVALID, "reference %u: materialIndex %u out of range", t, r.materialIndex);
+        NEED(r.lightTriangleIndex == MRT_NOT_A_LIGHT || r.lightTriangleIndex < light_count, MRT_E_INVALID, "reference %u: lightTriangleIndex out of range", t);
+    }
+    for (uint32_t l = 0; l < light_count; ++l) NEED(lights[l].index < triangle_count, MRT_E_INVALID, "light %u: index out of range", l);
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    free_scene(c);
+
+    BvhResult bvh;
+    build_bvh(vertices, indices, triangle_count, c->cfg.bvh_max_leaf, c->cfg.bvh_threads, bvh);
+    NEED(bvh.depth < MRT_STACK_DEPTH_HOST, MRT_E_INVALID, "BVH depth %u exceeds traversal stack", bvh.depth);
+
+    // shading records: vertices gathered per triangle through TriangleReference.tri (Shaders.metal:129,140)
+    std::vector<float> shade(20 * (size_t)std::max(1u, triangle_count), 0.0f);
+    for (uint32_t t = 0; t < triangle_count; ++t) {
+        float* s = &shade[20 * (size_t)t];
+        const mrt_triangle_reference& r = references[t];
+        for (int k = 0; k < 3; ++k) { std::memcpy(s + 3 * k, vertices[r.tri[k]].v, 12); std::memcpy(s + 9 + 3 * k, vertices[r.tri[k]].n, 12); }
+        std::memcpy(s + 18, &r.materialIndex, 4); std::memcpy(s + 19, &r.lightTriangleIndex, 4);
+    }
+    std::vector<float> mats(8 * (size_t)std::max(1u, material_count), 0.0f);
+    for (uint32_t m = 0; m < material_count; ++m) std::memcpy(&mats[8 * (size_t)m], &materials[m], 32);
+    std::vector<float> lts(24 * (size_t)(light_count + 1), 0.0f), cdf(light_count + 1);
+    for (uint32_t l = 0; l <= light_count; ++l) {
+        const mrt_light_triangle& L = lights[l];
+        float* p = &lts[24 * (size_t)l];
+        std::memcpy(p, L.emissive.values, 12); p[3] = L.area;
+        std::memcpy(p + 4, L.v1.v, 12); p[7] = L.pdf;
+        std::memcpy(p + 8, L.v1.n, 12); std::memcpy(p + 11, &L.index, 4);
+        std::memcpy(p + 12, L.v2.v, 12); std::memcpy(p + 15, L.v2.n, 12);
+        std::memcpy(p + 18, L.v3.v, 12); std::memcpy(p + 21, L.v3.n, 12);
+        cdf[l] = L.cdf;
+    }
+    auto upload = [&](void** dst, const void* src, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(dst, std::max<size_t>(bytes, 16));
+        if (e != cudaSuccess) return e;
+        return bytes ? cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice) : cudaSuccess;
+    };
+    CK(upload(&c->dNodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(BvhNode)));
+    CK(upload(&c->dTris, bvh.tris.data(), bvh.tris.size() * sizeof(BvhTri)));
+    CK(upload(&c->dShade, shade.data(), shade.size() * 4));
+    CK(upload(&c->dMats, mats.data(), mats.size() * 4));
+    CK(upload(&c->dLights, lts.data(), lts.size() * 4));
+    CK(upload(&c->dCdf, cdf.data(), cdf.size() * 4));
+    c->S.nodes = (const float4*)c->dNodes; c->S.tris = (const float4*)c->dTris; c->S.shadeTris = (const float4*)c->dShade;
+    c->S.materials = (const float4*)c->dMats; c->S.lights = (const float4*)c->dLights; c->S.lightCdf = (const float*)c->dCdf;
+    c->S.lightCount = light_count; c->S.triangleCount = triangle_count;
+    c->stats.bvh_nodes = (uint32_t)bvh.nodes.size(); c->stats.bvh_depth = bvh.depth; c->stats.bvh_sah_cost = bvh.sah_cost;
+    c->stats.bvh_build_ms = (float)bvh.build_ms;
+    c->haveScene = true;
+    return MRT_OK;
+}
+
+int mrt_set_scene_from(mrt_ctx* c, const mrt_scene* s) {
+    NEED(c && s, MRT_E_INVALID, "NULL argument");
+    return mrt_set_scene(c, s->vertices.data(), (uint32_t)s->vertices.size(), s->indices.data(), (uint32_t)s->references.size(),
+                         s->references.data(), s->materials.data(), (uint32_t)s->materials.size(), s->lights.data(), s->light_count);
+}
+
+int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
+    NEED(c, MRT_E_INVALID, "ctx is NULL");
+    NEED(width >= 2 && height >= 2, MRT_E_INVALID, "width and height must be >= 2 (raygen divides by size-1, Shaders.metal:92-94)");
+    NEED((uint64_t)width * height < (1ull << 31), MRT_E_INVALID, "too many rays");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    free_sized(c);
+    size_t n = (size_t)width * height;
+    CK(cudaMalloc(&c->dRays, n * sizeof(mrt_ray)));
+    CK(cudaMalloc(&c->dLightRays, n * sizeof(mrt_light_sampling_ray)));
+    CK(cudaMalloc(&c->dIsects, n * sizeof(mrt_intersection)));
+    CK(cudaMalloc(&c->dImage, n * sizeof(float4)));
+    CK(cudaMemsetAsync(c->dRays, 0, n * sizeof(mrt_ray), c->stream));                    // new MTLBuffers are zero-filled
+    CK(cudaMemsetAsync(c->dLightRays, 0, n * sizeof(mrt_light_sampling_ray), c->stream));
+    CK(cudaMemsetAsync(c->dIsects, 0, n * sizeof(mrt_intersection), c->stream));
+    CK(cudaMemsetAsync(c->dImage, 0, n * sizeof(float4), c->stream));
+    c->W = width; c->H = height;
+    return MRT_OK;
+}
+
+int mrt_set_noise(mrt_ctx* c, uint32_t slot, const float* tile) {
+    NEED(c && tile, MRT_E_INVALID, "NULL argument");
+    NEED(slot < MRT_NOISE_SLOTS, MRT_E_INVALID, "slot %u out of range", slot);
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(c->dNoisePool + slot * kTileFloat4, tile, kTileBytes, cudaMemcpyHostToDevice, c->stream));
+    return MRT_OK;
+}
+
+int mrt_set_row_shard(mrt_ctx* c, uint32_t first_row, uint32_t row_stride) {
+    NEED(c, MRT_E_INVALID, "ctx is NULL");
+    NEED(row_stride >= 1 && first_row < row_stride, MRT_E_INVALID, "need row_stride >= 1 and first_row < row_stride");
+    c->rowFirst = first_row; c->rowStride = row_stride;
+    return MRT_OK;
+}
+int mrt_set_accumulate_mode(mrt_ctx* c, uint32_t mode) {
+    NEED(c && mode <= MRT_ACCUM_REPLACE, MRT_E_INVALID, "bad accumulate mode");
+    c->cfg.accumulate_mode = mode;
+    return MRT_OK;
+}
+int mrt_set_pipeline(mrt_ctx* c, uint32_t pipeline) {
+    NEED(c && pipeline <= MRT_PIPELINE_WAVEFRONT, MRT_E_INVALID, "bad pipeline");
+    c->cfg.pipeline = pipeline;
+    return MRT_OK;
+}
+
+}  // extern "C"
+
+// ---- stage entry points, frame rendering, read-back -------------------------------------------------------------
+#define NEED_READY(c) do { NEED(c, MRT_E_INVALID, "ctx is NULL"); NEED((c)->haveScene, MRT_E_STATE, "no scene: call mrt_set_scene first"); \
+    NEED((c)->dRays, MRT_E_STATE, "no size: call mrt_resize first"); CK(cudaSetDevice((c)->cfg.device)); } while (0)
+#define LAUNCHED(c, n) do { (c)->stats.kernel_launches += (n); CK(cudaGetLastError()); } while (0)
+
+static inline const float4* slot_tile(const mrt_ctx* c, uint32_t slot) { return c->dNoisePool + (slot % MRT_NOISE_SLOTS) * kTileFloat4; }
+
+extern "C" {
+
+int mrt_raygen(mrt_ctx* c, uint32_t frame_index) {
+    NEED_READY(c);
+    launch_raygen(c->stream, c->dRays, slot_tile(c, frame_index), c->grid());               // Renderer.mm:508-512
+    LAUNCHED(c, 1);
+    return MRT_OK;
+}
+
+int mrt_intersect(mrt_ctx* c, uint32_t which) {
+    NEED_READY(c);
+    NEED(which == MRT_BUF_RAYS || which == MRT_BUF_LIGHT_RAYS, MRT_E_INVALID, "mrt_intersect: which must be MRT_BUF_RAYS or MRT_BUF_LIGHT_RAYS");
+    const void* rays = which == MRT_BUF_RAYS ? (const void*)c->dRays : (const void*)c->dLightRays;
+    uint32_t stride = which == MRT_BUF_RAYS ? sizeof(mrt_ray) : sizeof(mrt_light_sampling_ray);  // setRayStride, Renderer.mm:519,545
+    unsigned long long* live = c->cfg.count_rays ? c->dCounters + (which == MRT_BUF_RAYS ? 0 : 1) : nullptr;
+    launch_intersect(c->stream, c->S, rays, stride, c->W * c->H, c->dIsects, c->grid(), true, live, nullptr);
+    LAUNCHED(c, 1);
+    return MRT_OK;
+}
+
+int mrt_shade(mrt_ctx* c, uint32_t frame_index, uint32_t bounce_iteration) {
+    NEED_READY(c);
+    launch_shade(c->stream, c->S, c->dIsects, c->dRays, c->dLightRays, slot_tile(c, frame_index + bounce_iteration),  // Renderer.mm:538
+                 frame_index, c->cfg.max_path_length, c->grid());
+    LAUNCHED(c, 1);
+    return MRT_OK;
+}
+
+int mrt_shadow_resolve(mrt_ctx* c) {
+    NEED_READY(c);
+    launch_shadow_resolve(c->stream, c->dIsects, c->dRays, c->dLightRays, c->grid());
+    LAUNCHED(c, 1);
+    return MRT_OK;
+}
+
+int mrt_accumulate(mrt_ctx* c, uint32_t frame_index) {
+    NEED_READY(c);
+    launch_accumulate(c->stream, c->dImage, c->dRays, frame_index, c->cfg.accumulate_mode, c->grid());
+    LAUNCHED(c, 1);
+    return MRT_OK;
+}
+
+// Renderer.mm:504-584: 1 + 4*L + 1 dispatches
+int mrt_render_frame_staged(mrt_ctx* c, uint32_t frame_index) {
+    int rc = mrt_raygen(c, frame_index);
+    for (uint32_t i = 0; rc == MRT_OK && i < c->cfg.max_path_length; ++i) {
+        if ((rc = mrt_intersect(c, MRT_BUF_RAYS))) break;
+        if ((rc = mrt_shade(c, frame_index, i))) break;
+        if ((rc = mrt_intersect(c, MRT_BUF_LIGHT_RAYS))) break;
+        rc = mrt_shadow_resolve(c);
+    }
+    if (rc == MRT_OK) rc = mrt_accumulate(c, frame_index);
+    if (rc == MRT_OK) c->stats.frames_rendered += 1;
+    return rc;
+}
+
+int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint32_t frame_stride, const float* noise_tiles) {
+    NEED_READY(c);
+    if (n_frames == 0) return MRT_OK;
+    if (frame_stride == 0) frame_stride = 1;
+    NEED((uint64_t)first_frame + (uint64_t)(n_frames - 1) * frame_stride < 0xFFFFFFFFull, MRT_E_INVALID, "frame index overflow");
+    const uint32_t span = (n_frames - 1) * frame_stride + 1;              // tiles supplied: one per frame first..last
+    const bool refresh = noise_tiles != nullptr && c->cfg.animate_noise;
+    CK(cudaEventRecord(c->ev0, c->stream));
+
+    if (c->cfg.pipeline == MRT_PIPELINE_WAVEFRONT) {
+        // the reference's own shape: per frame refresh slot f%3 (Renderer.mm:492-496), then 2 + 4*L dispatches
+        for (uint32_t k = 0; k < span; ++k) {
+            uint32_t f = first_frame + k;
+            if (refresh) CK(cudaMemcpyAsync(c->dNoisePool + (f % 3u) * kTileFloat4, noise_tiles + (size_t)k * MRT_NOISE_TILE_FLOATS, kTileBytes,
+                                            cudaMemcpyHostToDevice, c->stream));
+            if (k % frame_stride == 0) { int rc = mrt_render_frame_staged(c, f); if (rc) return rc; }
+        }
+    } else {
+        int rc = ensure_pool(c, MRT_NOISE_SLOTS + (refresh ? span : 0));
+        if (rc) return rc;
+        rc = ensure_table(c, n_frames);
+        if (rc) return rc;
+        if (refresh) CK(cudaMemcpyAsync(c->dNoisePool + MRT_NOISE_SLOTS * kTileFloat4, noise_tiles, (size_t)span * kTileBytes,
+                                        cudaMemcpyHostToDevice, c->stream));
+        CK(cudaEventSynchronize(c->tableCopied));                         // previous batch's table has left the pinned buffer
+        uint32_t slotTile[3] = {0, 1, 2};
+        uint32_t e = 0;
+        for (uint32_t k = 0; k < span; ++k) {
+            uint32_t f = first_frame + k;
+            if (refresh) slotTile[f % 3u] = MRT_NOISE_SLOTS + k;
+            if (k % frame_stride == 0) { FrameEntry& fe = c->hFrameTable[e++]; fe.frame = f; fe.tile[0] = slotTile[0]; fe.tile[1] = slotTile[1]; fe.tile[2] = slotTile[2]; }
+        }
+        CK(cudaMemcpyAsync(c->dFrameTable, c->hFrameTable, n_frames * sizeof(FrameEntry), cudaMemcpyHostToDevice, c->stream));
+        CK(cudaEventRecord(c->tableCopied, c->stream));
+        RenderParams p;
+        p.S = c->S; p.noisePool = c->dNoisePool; p.frames = c->dFrameTable; p.nFrames = n_frames; p.image = c->dImage;
+        p.g = c->grid(); p.ownedRows = c->ownedRows(); p.maxPathLength = c->cfg.max_path_length; p.accumMode = c->cfg.accumulate_mode;
+        p.counters = c->dCounters;
+        launch_render_fused(c->stream, p, c->cfg.count_rays != 0);
+        LAUNCHED(c, 1);
+        // leave the three slots as the reference's would be after the last frame
+        for (uint32_t s = 0; s < 3 && refresh; ++s)
+            if (slotTile[s] != s) CK(cudaMemcpyAsync(c->dNoisePool + s * kTileFloat4, c->dNoisePool + slotTile[s] * kTileFloat4, kTileBytes,
+                                                     cudaMemcpyDeviceToDevice, c->stream));
+        c->stats.frames_rendered += n_frames;
+    }
+    CK(cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    return MRT_OK;
+}
+
+int mrt_sync(mrt_ctx* c) {
+    NEED(c, MRT_E_INVALID, "ctx is NULL");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    return MRT_OK;
+}
+
+int mrt_read_image(mrt_ctx* c, float* rgba) {
+    NEED(c && rgba, MRT_E_INVALID, "NULL argument");
+    NEED(c->dImage, MRT_E_STATE, "no size: call mrt_resize first");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(rgba, c->dImage, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return MRT_OK;
+}
+int mrt_scale_image(mrt_ctx* c, float scale) {
+    NEED(c && c->dImage, MRT_E_STATE, "no image");
+    CK(cudaSetDevice(c->cfg.device));
+    launch_scale_image(c->stream, c->dImage, scale, c->W * c->H);
+    LAUNCHED(c, 1);
+    return MRT_OK;
+}
+int mrt_clear_image(mrt_ctx* c) {
+    NEED(c && c->dImage, MRT_E_STATE, "no image");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemsetAsync(c->dImage, 0, (size_t)c->W * c->H * sizeof(float4), c->stream));
+    return MRT_OK;
+}
+int mrt_image_device_ptr(mrt_ctx* c, void** device_ptr, size_t* bytes) {
+    NEED(c && device_ptr && c->dImage, MRT_E_STATE, "no image");
+    *device_ptr = c->dImage;
+    if (bytes) *bytes = (size_t)c->W * c->H * sizeof(float4);
+    return MRT_OK;
+}
+
+static int buffer_of(mrt_ctx* c, uint32_t which, void** p, size_t* bytes) {
+    size_t n = (size_t)c->W * c->H;
+    switch (which) {
+        case MRT_BUF_RAYS: *p = c->dRays; *bytes = n * sizeof(mrt_ray); return MRT_OK;
+        case MRT_BUF_LIGHT_RAYS: *p = c->dLightRays; *bytes = n * sizeof(mrt_light_sampling_ray); return MRT_OK;
+        case MRT_BUF_INTERSECTIONS: *p = c->dIsects; *bytes = n * sizeof(mrt_intersection); return MRT_OK;
+        case MRT_BUF_IMAGE: *p = c->dImage; *bytes = n * sizeof(float4); return MRT_OK;
+    }
+    return fail(MRT_E_INVALID, "unknown buffer %u", which);
+}
+int mrt_read_buffer(mrt_ctx* c, uint32_t which, void* dst, size_t bytes) {
+    NEED(c && dst && c->dRays, MRT_E_STATE, "no buffers: call mrt_resize first");
+    void* p = nullptr; size_t cap = 0; int rc = buffer_of(c, which, &p, &cap); if (rc) return rc;
+    NEED(bytes <= cap, MRT_E_INVALID, "read of %zu bytes exceeds buffer (%zu)", bytes, cap);
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(dst, p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return MRT_OK;
+}
+int mrt_write_buffer(mrt_ctx* c, uint32_t which, const void* src, size_t bytes) {
+    NEED(c && src && c->dRays, MRT_E_STATE, "no buffers: call mrt_resize first");
+    void* p = nullptr; size_t cap = 0; int rc = buffer_of(c, which, &p, &cap); if (rc) return rc;
+    NEED(bytes <= cap, MRT_E_INVALID, "write of %zu bytes exceeds buffer (%zu)", bytes, cap);
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(p, src, bytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return MRT_OK;
+}
+
+int mrt_get_stats(mrt_ctx* c, mrt_stats* out) {
+    NEED(c && out, MRT_E_INVALID, "NULL argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    unsigned long long h[4];
+    CK(cudaMemcpy(h, c->dCounters, sizeof h, cudaMemcpyDeviceToHost));
+    c->stats.primary_rays = h[0]; c->stats.shadow_rays = h[1]; c->stats.nodes_visited = h[2]; c->stats.triangles_tested = h[3];
+    if (c->timed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->ev0, c->ev1)); c->stats.last_render_ms = ms; }
+    *out = c->stats;
+    return MRT_OK;
+}
+int mrt_reset_stats(mrt_ctx* c) {
+    NEED(c, MRT_E_INVALID, "ctx is NULL");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemsetAsync(c->dCounters, 0, 4 * sizeof(unsigned long long), c->stream));
+    c->stats.kernel_launches = 0; c->stats.frames_rendered = 0;
+    return MRT_OK;
+}
+
+static int intersect_host_impl(mrt_ctx* c, const void* rays, size_t stride, uint32_t count, mrt_intersection* out, bool profile) {
+    NEED(c && rays, MRT_E_INVALID, "NULL argument");
+    NEED(c->haveScene, MRT_E_STATE, "no scene: call mrt_set_scene first");
+    NEED(stride >= 32 && stride % 4 == 0, MRT_E_INVALID, "ray stride must be >= 32 and a multiple of 4");
+    if (count == 0) return MRT_OK;
+    CK(cudaSetDevice(c->cfg.device));
+    void* dR = nullptr; mrt_intersection* dO = nullptr;
+    CK(cudaMalloc(&dR, (size_t)count * stride));
+    CK(cudaMalloc(&dO, (size_t)count * sizeof(mrt_intersection)));
+    CK(cudaMemcpyAsync(dR, rays, (size_t)count * stride, cudaMemcpyHostToDevice, c->stream));
+    Grid2D g; g.W = count; g.H = 1; g.rowFirst = 0; g.rowStride = 1;
+    launch_intersect(c->stream, c->S, dR, (uint32_t)stride, count, dO, g, false, nullptr, profile ? c->dCounters + 2 : nullptr);
+    c->stats.kernel_launches += 1;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess && out) e = cudaMemcpyAsync(out, dO, (size_t)count * sizeof(mrt_intersection), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(dR); cudaFree(dO);
+    if (e != cudaSuccess) return fail(MRT_E_CUDA, "mrt_intersect_host: %s", cudaGetErrorString(e));
+    return MRT_OK;
+}
+int mrt_intersect_host(mrt_ctx* c, const void* rays, size_t stride_bytes, uint32_t count, mrt_intersection* out) {
+    NEED(out, MRT_E_INVALID, "out is NULL");
+    return intersect_host_impl(c, rays, stride_bytes, count, out, false);
+}
+int mrt_profile_traversal(mrt_ctx* c, const void* rays, size_t stride_bytes, uint32_t count) {
+    return intersect_host_impl(c, rays, stride_bytes, count, nullptr, true);
+}
+
+// ---- caller-side helpers (host only) -------------------------------------------------------------------------
+int mrt_scene_create_procedural(const char* name, uint64_t seed, mrt_scene** out) {
+    NEED(name && out, MRT_E_INVALID, "NULL argument");
+    mrt_scene* s = new (std::nothrow) mrt_scene();
+    NEED(s, MRT_E_NOMEM, "out of host memory");
+    std::string err;
+    if (!make_procedural(name, seed, *s, err)) { delete s; return fail(MRT_E_INVALID, "%s", err.c_str()); }
+    *out = s;
+    return MRT_OK;
+}
+int mrt_scene_load_obj(const char* obj_path, mrt_scene** out) {
+    NEED(obj_path && out, MRT_E_INVALID, "NULL argument");
+    mrt_scene* s = new (std::nothrow) mrt_scene();
+    NEED(s, MRT_E_NOMEM, "out of host memory");
+    std::string err;
+    if (!load_obj(obj_path, *s, err)) { delete s; return fail(MRT_E_IO, "%s", err.c_str()); }
+    *out = s;
+    return MRT_OK;
+}
+int mrt_scene_get(const mrt_scene* s, mrt_scene_view* v) {
+    NEED(s && v, MRT_E_INVALID, "NULL argument");
+    v->vertices = s->vertices.data(); v->vertex_count = (uint32_t)s->vertices.size();
+    v->indices = s->indices.data(); v->triangle_count = (uint32_t)s->references.size();
+    v->references = s->references.data();
+    v->materials = s->materials.data(); v->material_count = (uint32_t)s->materials.size();
+    v->lights = s->lights.data(); v->light_count = s->light_count;
+    return MRT_OK;
+}
+void mrt_scene_destroy(mrt_scene* s) { delete s; }
+void mrt_noise_fill(uint64_t seed, uint32_t frame, float* tile) { noise_fill(seed, frame, tile); }
+
+}  // extern "C"

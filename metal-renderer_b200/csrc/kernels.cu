@@ -1,0 +1,266 @@
+// kernels.cu — sm_100a kernels of the per-pixel pipeline raygen -> intersect -> shade/NEE -> shadow intersect ->
+// resolve -> accumulate (reference: renderer/Shaders.metal:75-249 sequenced by renderer/Renderer.mm:500-585).
+//
+// Two forms of the same arithmetic (device_shading.cuh / device_trace.cuh):
+//   * stage kernels that keep the reference's buffers and stage boundaries (drop-in + test seams), and
+//   * the fused megakernel: one launch renders whole frames with the path state in registers, lanes that finish
+//     a sample start the next one at once, and primary and shadow rays share one traversal site.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false (see device_math.cuh for why).
+#include "kernels.h"
+#include "device_trace.cuh"
+
+namespace mrt {
+
+__device__ __forceinline__ bool owns_row(const Grid2D& g, uint32_t y) { return y % g.rowStride == g.rowFirst; }
+
+// ---- rayGenerator (Shaders.metal:75-103) -----------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_raygen(mrt_ray* __restrict__ rays, const float4* __restrict__ noise, Grid2D g) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.W * g.H) return;
+    uint32_t x = i % g.W, y = i / g.W;
+    if (!owns_row(g, y)) return;
+    PathState st;
+    ray_generator(st, noise, x, y, g.W, g.H);
+    float4* r = reinterpret_cast<float4*>(rays + i);
+    float minDistance = rays[i].minDistance;               // never written by the reference; keep what is there
+    r[0] = make_float4(st.origin.x, st.origin.y, st.origin.z, minDistance);
+    r[1] = make_float4(st.direction.x, st.direction.y, st.direction.z, INFINITY);
+    rays[i].throughput.values[0] = 1.0f; rays[i].throughput.values[1] = 1.0f; rays[i].throughput.values[2] = 1.0f;
+    rays[i].radiance.values[0] = 0.0f; rays[i].radiance.values[1] = 0.0f; rays[i].radiance.values[2] = 0.0f;
+    r[4] = make_float4(st.pdf, st.prevDiffuse, st.bounce, st.ior);
+}
+
+// ---- MPS nearest-hit stand-in over a strided ray buffer (Renderer.mm:519-523, 545-553) -------------------
+template <bool VEC, bool COUNT>
+__global__ void __launch_bounds__(256) k_intersect(DeviceScene S, const char* __restrict__ rays, uint32_t stride, uint32_t count,
+                                                   mrt_intersection* __restrict__ out, Grid2D g, bool useGrid,
+                                                   unsigned long long* liveCounter, unsigned long long* visitCounters) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long nodesV = 0, trisT = 0;
+    uint32_t live = 0;
+    if (i < count && (!useGrid || owns_row(g, i / g.W))) {
+        const char* p = rays + (size_t)i * stride;
+        float4 a, b;
+        if (VEC) { a = *reinterpret_cast<const float4*>(p); b = *reinterpret_cast<const float4*>(p + 16); }
+        else {
+            const float* f = reinterpret_cast<const float*>(p);
+            a = make_float4(f[0], f[1], f[2], f[3]); b = make_float4(f[4], f[5], f[6], f[7]);
+        }
+        HitRec h; h.t = -1.0f; h.tri = MRT_NO_HIT; h.u = 0.0f; h.v = 0.0f;
+        if (b.w >= 0.0f) {                                 // rays with a negative maxDistance are skipped
+            live = 1;
+            h = trace_nearest<COUNT>(S.nodes, S.tris, mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), a.w, b.w, &nodesV, &trisT);
+        }
+        *reinterpret_cast<float4*>(out + i) = make_float4(h.t, __uint_as_float(h.tri), h.u, h.v);
+    }
+    if (liveCounter) {
+        uint32_t n = __reduce_add_sync(0xffffffffu, live);
+        if ((threadIdx.x & 31) == 0 && n) atomicAdd(liveCounter, (unsigned long long)n);
+    }
+    if (COUNT) {
+        for (int o = 16; o; o >>= 1) { nodesV += __shfl_xor_sync(0xffffffffu, nodesV, o); trisT += __shfl_xor_sync(0xffffffffu, trisT, o); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(visitCounters, nodesV); atomicAdd(visitCounters + 1, trisT); }
+    }
+}
+
+// ---- intersectionHandler (Shaders.metal:105-212) ----------------------------------------------------------
+__global__ void __launch_bounds__(256) k_shade(DeviceScene S, const mrt_intersection* __restrict__ isects, mrt_ray* __restrict__ rays,
+                                               mrt_light_sampling_ray* __restrict__ lightRays, const float4* __restrict__ noise,
+                                               uint32_t frameIndex, uint32_t maxPathLength, Grid2D g) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.W * g.H) return;
+    uint32_t x = i % g.W, y = i / g.W;
+    if (!owns_row(g, y)) return;
+    lightRays[i].maxDistance = -1.0f;                                                   // :119
+    float4 is = *reinterpret_cast<const float4*>(isects + i);
+    if (is.x < MRT_DISTANCE_EPSILON) { rays[i].maxDistance = -1.0f; return; }            // :122-126
+    float4* r = reinterpret_cast<float4*>(rays + i);
+    float4 r0 = r[0], r1 = r[1], r2 = r[2], r3 = r[3], r4 = r[4];
+    PathState st;
+    st.origin = mk3(r0.x, r0.y, r0.z); st.direction = mk3(r1.x, r1.y, r1.z);
+    st.throughput = mk3(r2.x, r2.y, r2.z); st.radiance = mk3(r2.w, r3.x, r3.y);
+    st.pdf = r4.x; st.prevDiffuse = r4.y; st.bounce = r4.z; st.ior = r4.w;
+    HitRec hit; hit.t = is.x; hit.tri = __float_as_uint(is.y); hit.u = is.z; hit.v = is.w;
+    ShadowRay sh; bool nee;
+    bool live = intersection_handler(S, hit, st, sh, nee, noise, frameIndex, maxPathLength, x, y);
+    if (nee) {                                                                          // :171-175
+        float4* l = reinterpret_cast<float4*>(lightRays + i);
+        float lmin = lightRays[i].minDistance;
+        l[0] = make_float4(st.origin.x, st.origin.y, st.origin.z, lmin);
+        l[1] = make_float4(sh.direction.x, sh.direction.y, sh.direction.z, live ? INFINITY : -1.0f);
+        l[2] = make_float4(sh.throughput.x, sh.throughput.y, sh.throughput.z, __uint_as_float(sh.targetIndex));
+    }
+    r[0] = make_float4(st.origin.x, st.origin.y, st.origin.z, r0.w);
+    r[1] = make_float4(st.direction.x, st.direction.y, st.direction.z, INFINITY);
+    r[2] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.radiance.x);
+    r[3] = make_float4(st.radiance.y, st.radiance.z, r3.z, r3.w);
+    r[4] = make_float4(st.pdf, st.prevDiffuse, st.bounce, st.ior);
+}
+
+// ---- lightSamplingHandler (Shaders.metal:214-231) -----------------------------------------------------------
+__global__ void __launch_bounds__(256) k_shadow_resolve(const mrt_intersection* __restrict__ isects, mrt_ray* __restrict__ rays,
+                                                        const mrt_light_sampling_ray* __restrict__ lightRays, Grid2D g) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.W * g.H || !owns_row(g, i / g.W)) return;
+    float4 is = *reinterpret_cast<const float4*>(isects + i);
+    float4 l2 = reinterpret_cast<const float4*>(lightRays + i)[2];
+    if (is.x >= MRT_DISTANCE_EPSILON && __float_as_uint(is.y) == __float_as_uint(l2.w)) {
+        rays[i].radiance.values[0] += l2.x; rays[i].radiance.values[1] += l2.y; rays[i].radiance.values[2] += l2.z;
+    }
+}
+
+// ---- accumulateImage (Shaders.metal:233-249) ----------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_accumulate(float4* __restrict__ image, const mrt_ray* __restrict__ rays, uint32_t frameIndex,
+                                                    uint32_t mode, Grid2D g) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.W * g.H || !owns_row(g, i / g.W)) return;
+    f3 color = mk3(rays[i].radiance.values[0], rays[i].radiance.values[1], rays[i].radiance.values[2]);
+    float4 stored = image[i];
+    color = accumulate_image(color, mk3(stored.x, stored.y, stored.z), frameIndex, mode);
+    image[i] = make_float4(color.x, color.y, color.z, 1.0f);
+}
+
+__global__ void __launch_bounds__(256) k_scale_image(float4* __restrict__ image, float scale, uint32_t count) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    float4 c = image[i];
+    image[i] = make_float4(c.x * scale, c.y * scale, c.z * scale, 1.0f);
+}
+
+// ---- fused megakernel ----------------------------------------------------------------------------------------
+// One thread owns one pixel for every frame of the batch; a warp owns an 8x4 pixel tile.  Per lane a small state
+// machine runs GEN -> (PRIMARY -> [SHADOW])* -> GEN ...: a lane whose sample ends (path died or reached
+// maxPathLength) accumulates it and generates the next frame's camera ray in the same iteration, so every
+// traversal sees a full set of live rays, and primary and shadow rays go through ONE traversal site.  The
+// sequence of float operations per pixel is exactly the stage sequence of Renderer.mm:504-584.
+enum { PH_GEN = 0, PH_PRIMARY = 1, PH_SHADOW = 2 };
+
+template <bool COUNT>
+__global__ void __launch_bounds__(256, 2) k_render_fused(RenderParams P) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t tilesX = (P.g.W + 7u) >> 3;
+    const uint32_t tx = warp % tilesX, ty = warp / tilesX;
+    const uint32_t x = tx * 8u + (lane & 7u);
+    const uint32_t row = ty * 4u + (lane >> 3);
+    const uint32_t y = P.g.rowFirst + row * P.g.rowStride;
+    bool done = !(x < P.g.W && row < P.ownedRows);
+    const uint32_t pix = done ? 0u : y * P.g.W + x;
+
+    f3 color = mk3(0.0f, 0.0f, 0.0f);
+    if (!done) { float4 c = P.image[pix]; color = mk3(c.x, c.y, c.z); }
+    PathState st; ShadowRay sh;
+    st.origin = st.direction = st.throughput = st.radiance = mk3(0.0f, 0.0f, 0.0f);
+    st.pdf = st.prevDiffuse = st.bounce = st.ior = 0.0f;
+    sh.direction = sh.throughput = mk3(0.0f, 0.0f, 0.0f); sh.targetIndex = 0;
+    uint32_t phase = PH_GEN, k = 0, frame = 0, tile0 = 0, tile1 = 0, tile2 = 0;
+    uint32_t nPrimary = 0, nShadow = 0;
+    unsigned long long dummyA = 0, dummyB = 0;
+    const size_t tileStride = MRT_NOISE_DIMENSIONS * MRT_NOISE_DIMENSIONS;
+
+    for (;;) {
+        if (!done && phase == PH_GEN) {
+            if (k == P.nFrames) {
+                P.image[pix] = make_float4(color.x, color.y, color.z, 1.0f);
+                done = true;
+            } else {
+                uint4 e = __ldg(P.frames + k);
+                ++k;
+                frame = e.x; tile0 = e.y; tile1 = e.z; tile2 = e.w;
+                uint32_t slot = frame % 3u;
+                uint32_t t = slot == 0 ? tile0 : (slot == 1 ? tile1 : tile2);
+                ray_generator(st, P.noisePool + t * tileStride, x, y, P.g.W, P.g.H);      // Renderer.mm:508-512
+                phase = PH_PRIMARY;
+            }
+        }
+        if (__all_sync(0xffffffffu, done)) break;
+        if (done) continue;
+
+        const f3 dir = phase == PH_PRIMARY ? st.direction : sh.direction;
+        HitRec hit = trace_nearest<false>(P.S.nodes, P.S.tris, st.origin, dir, 0.0f, INFINITY, &dummyA, &dummyB);
+
+        bool finished = false;
+        if (phase == PH_PRIMARY) {
+            if (COUNT) ++nPrimary;
+            if (hit.t < MRT_DISTANCE_EPSILON) {                                        // Shaders.metal:122-126
+                finished = true;
+            } else {
+                uint32_t bounce = uint32_t(st.bounce);
+                uint32_t slot = (frame + bounce) % 3u;                                  // Renderer.mm:538
+                uint32_t t = slot == 0 ? tile0 : (slot == 1 ? tile1 : tile2);
+                bool nee;
+                bool live = intersection_handler(P.S, hit, st, sh, nee, P.noisePool + t * tileStride, frame,
+                                                 P.maxPathLength, x, y);
+                if (live) phase = PH_SHADOW;
+                else finished = uint32_t(st.bounce) >= P.maxPathLength;
+            }
+        } else {
+            if (COUNT) ++nShadow;
+            if (hit.t >= MRT_DISTANCE_EPSILON && hit.tri == sh.targetIndex)             // Shaders.metal:225-229
+                st.radiance = st.radiance + sh.throughput;
+            phase = PH_PRIMARY;
+            finished = uint32_t(st.bounce) >= P.maxPathLength;
+        }
+        if (finished) {
+            color = accumulate_image(st.radiance, color, frame, P.accumMode);          // Shaders.metal:239-248
+            phase = PH_GEN;
+        }
+    }
+    if (COUNT) {
+        uint32_t a = __reduce_add_sync(0xffffffffu, nPrimary), b = __reduce_add_sync(0xffffffffu, nShadow);
+        if (lane == 0) { atomicAdd(P.counters, (unsigned long long)a); atomicAdd(P.counters + 1, (unsigned long long)b); }
+    }
+}
+
+// ---- launchers -----------------------------------------------------------------------------------------------
+static inline uint32_t blocks_for(uint32_t n) { return (n + 255u) / 256u; }
+
+void launch_raygen(cudaStream_t s, mrt_ray* rays, const float4* noiseTile, Grid2D g) {
+    k_raygen<<<blocks_for(g.W * g.H), 256, 0, s>>>(rays, noiseTile, g);
+}
+void launch_intersect(cudaStream_t s, const DeviceScene& S, const void* rays, uint32_t strideBytes, uint32_t count,
+                      mrt_intersection* out, Grid2D g, bool useGrid, unsigned long long* liveCounter,
+                      unsigned long long* visitCounters) {
+    if (count == 0) return;
+    bool vec = (strideBytes % 16u == 0) && ((uintptr_t)rays % 16u == 0);
+    const char* r = static_cast<const char*>(rays);
+    if (visitCounters) {
+        if (vec) k_intersect<true, true><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, liveCounter, visitCounters);
+        else k_intersect<false, true><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, liveCounter, visitCounters);
+    } else {
+        if (vec) k_intersect<true, false><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, liveCounter, nullptr);
+        else k_intersect<false, false><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, liveCounter, nullptr);
+    }
+}
+void launch_shade(cudaStream_t s, const DeviceScene& S, const mrt_intersection* isects, mrt_ray* rays,
+                  mrt_light_sampling_ray* lightRays, const float4* noiseTile, uint32_t frameIndex, uint32_t maxPathLength,
+                  Grid2D g) {
+    k_shade<<<blocks_for(g.W * g.H), 256, 0, s>>>(S, isects, rays, lightRays, noiseTile, frameIndex, maxPathLength, g);
+}
+void launch_shadow_resolve(cudaStream_t s, const mrt_intersection* isects, mrt_ray* rays,
+                           const mrt_light_sampling_ray* lightRays, Grid2D g) {
+    k_shadow_resolve<<<blocks_for(g.W * g.H), 256, 0, s>>>(isects, rays, lightRays, g);
+}
+void launch_accumulate(cudaStream_t s, float4* image, const mrt_ray* rays, uint32_t frameIndex, uint32_t mode, Grid2D g) {
+    k_accumulate<<<blocks_for(g.W * g.H), 256, 0, s>>>(image, rays, frameIndex, mode, g);
+}
+void launch_scale_image(cudaStream_t s, float4* image, float scale, uint32_t count) {
+    k_scale_image<<<blocks_for(count), 256, 0, s>>>(image, scale, count);
+}
+void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays) {
+    uint32_t tilesX = (p.g.W + 7u) >> 3, tilesY = (p.ownedRows + 3u) >> 2;
+    uint32_t warps = tilesX * tilesY;
+    if (warps == 0 || p.nFrames == 0) return;
+    uint32_t blocks = (warps + 7u) / 8u;
+    if (countRays) k_render_fused<true><<<blocks, 256, 0, s>>>(p);
+    else k_render_fused<false><<<blocks, 256, 0, s>>>(p);
+}
+int fused_kernel_info(int* regs, int* maxBlocksPerSM) {
+    cudaFuncAttributes a;
+    cudaError_t e = cudaFuncGetAttributes(&a, k_render_fused<true>);
+    if (e != cudaSuccess) return (int)e;
+    *regs = a.numRegs;
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true>, 256, 0);
+}
+
+}  // namespace mrt

@@ -1,0 +1,175 @@
+"""Host-side mirror of the reference's `Renderer` object for the path-tracing path
+(reference renderer/Renderer.h:5-6, renderer/Renderer.mm).  Method names follow the reference's:
+
+    Renderer(...)                       -initWithMetalKitView: / -loadMetalWithView:   Renderer.mm:72-154
+    init_raytracing(scene)              -initRaytracing                               Renderer.mm:255-470
+    drawable_size_will_change(w, h)     -mtkView:drawableSizeWillChange:              Renderer.mm:640-657
+    update_noise(slot, tile)            noise part of -updateSharedData               Renderer.mm:485-497
+    perform_raytracing(frame)           -performRaytracing: (34 dispatches)           Renderer.mm:500-585
+    draw(n_frames, noise)               -drawInMTKView: loop, headless, fused kernel  Renderer.mm:587-638
+    save_current_image()                -saveCurrentImage (a stub in the reference)   Renderer.mm:659-662
+
+All computation happens in libmrt_b200.so on the GPU; this file only marshals arguments.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+from .scene import Scene
+
+
+class Renderer:
+    def __init__(self, device=0, max_path_length=8, accumulate_mode=L.ACCUM_MEAN, pipeline=L.PIPELINE_AUTO,
+                 animate_noise=True, count_rays=True, bvh_max_leaf=4, bvh_threads=0):
+        cfg = L.Config()
+        L.lib().mrt_config_default(C.byref(cfg))
+        cfg.device = device
+        cfg.max_path_length = max_path_length
+        cfg.accumulate_mode = accumulate_mode
+        cfg.pipeline = pipeline
+        cfg.animate_noise = int(animate_noise)
+        cfg.count_rays = int(count_rays)
+        cfg.bvh_max_leaf = bvh_max_leaf
+        cfg.bvh_threads = bvh_threads
+        self._ctx = C.c_void_p()
+        L.check(L.lib().mrt_create(C.byref(cfg), C.byref(self._ctx)))
+        self.width = self.height = 0
+        self.frame_index = 0
+        self.max_path_length = max_path_length
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            L.lib().mrt_destroy(self._ctx)
+            self._ctx = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ---- setup -----------------------------------------------------------------------------------------
+    def init_raytracing(self, scene: Scene):
+        L.check(L.lib().mrt_set_scene(self._ctx, L.ptr(scene.vertices), len(scene.vertices), L.ptr(scene.indices),
+                                      scene.triangle_count, L.ptr(scene.references), L.ptr(scene.materials),
+                                      len(scene.materials), L.ptr(scene.lights), scene.light_count))
+
+    def drawable_size_will_change(self, width, height):
+        L.check(L.lib().mrt_resize(self._ctx, width, height))
+        self.width, self.height = width, height
+        self.frame_index = 0
+
+    def update_noise(self, slot, tile):
+        tile = np.ascontiguousarray(tile, dtype=np.float32).reshape(-1)
+        assert tile.size == L.NOISE_TILE_FLOATS
+        L.check(L.lib().mrt_set_noise(self._ctx, slot, L.ptr(tile)))
+        L.check(L.lib().mrt_sync(self._ctx))          # tile is borrowed only for this call
+
+    def set_row_shard(self, first_row, row_stride):
+        L.check(L.lib().mrt_set_row_shard(self._ctx, first_row, row_stride))
+
+    def set_accumulate_mode(self, mode):
+        L.check(L.lib().mrt_set_accumulate_mode(self._ctx, mode))
+
+    def set_pipeline(self, pipeline):
+        L.check(L.lib().mrt_set_pipeline(self._ctx, pipeline))
+
+    # ---- the six dispatch kinds ------------------------------------------------------------------------
+    def raygen(self, frame):
+        L.check(L.lib().mrt_raygen(self._ctx, frame))
+
+    def intersect(self, which=L.BUF_RAYS):
+        L.check(L.lib().mrt_intersect(self._ctx, which))
+
+    def shade(self, frame, bounce_iteration):
+        L.check(L.lib().mrt_shade(self._ctx, frame, bounce_iteration))
+
+    def shadow_resolve(self):
+        L.check(L.lib().mrt_shadow_resolve(self._ctx))
+
+    def accumulate(self, frame):
+        L.check(L.lib().mrt_accumulate(self._ctx, frame))
+
+    def perform_raytracing(self, frame):
+        L.check(L.lib().mrt_render_frame_staged(self._ctx, frame))
+
+    # ---- production path -------------------------------------------------------------------------------
+    def draw(self, n_frames, noise_tiles=None, first_frame=None, frame_stride=1, sync=True):
+        """Render n_frames frames (first_frame, first_frame+stride, ...).  noise_tiles: float32 array of
+        (n_frames-1)*stride+1 tiles (tile k refreshes slot (first_frame+k)%3 before that frame), or None."""
+        first = self.frame_index if first_frame is None else first_frame
+        p = None
+        if noise_tiles is not None:
+            need = ((n_frames - 1) * frame_stride + 1) * L.NOISE_TILE_FLOATS if n_frames else 0
+            if isinstance(noise_tiles, np.ndarray):
+                assert noise_tiles.dtype == np.float32 and noise_tiles.flags["C_CONTIGUOUS"] and noise_tiles.size >= need
+                p = L.ptr(noise_tiles)
+            else:                                   # raw host address (e.g. a pinned torch tensor's data_ptr())
+                p = C.c_void_p(int(noise_tiles))
+        L.check(L.lib().mrt_render_frames(self._ctx, first, n_frames, frame_stride, p))
+        if n_frames:
+            self.frame_index = first + (n_frames - 1) * frame_stride + 1
+        if sync:
+            self.sync()
+
+    def sync(self):
+        L.check(L.lib().mrt_sync(self._ctx))
+
+    # ---- results ---------------------------------------------------------------------------------------
+    def save_current_image(self, out=None):
+        """RGBA32F image, shape (H, W, 4), row 0 = bottom row (as the reference's texture)."""
+        img = out if out is not None else np.empty((self.height, self.width, 4), dtype=np.float32)
+        L.check(L.lib().mrt_read_image(self._ctx, L.ptr(img)))
+        return img
+
+    def read_image_into(self, host_address):
+        L.check(L.lib().mrt_read_image(self._ctx, C.c_void_p(int(host_address))))
+
+    def scale_image(self, scale):
+        L.check(L.lib().mrt_scale_image(self._ctx, scale))
+
+    def clear_image(self):
+        L.check(L.lib().mrt_clear_image(self._ctx))
+
+    def image_device_ptr(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        L.check(L.lib().mrt_image_device_ptr(self._ctx, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def read_buffer(self, which):
+        n = self.width * self.height
+        if which == L.BUF_IMAGE:
+            out = np.empty((n, 4), dtype=np.float32)
+        else:
+            out = np.empty(n, dtype=L.BUFFER_DTYPES[which])
+        L.check(L.lib().mrt_read_buffer(self._ctx, which, L.ptr(out), out.nbytes))
+        return out
+
+    def write_buffer(self, which, array):
+        array = np.ascontiguousarray(array)
+        L.check(L.lib().mrt_write_buffer(self._ctx, which, L.ptr(array), array.nbytes))
+
+    def stats(self):
+        s = L.Stats()
+        L.check(L.lib().mrt_get_stats(self._ctx, C.byref(s)))
+        return {name: getattr(s, name) for name, _ in L.Stats._fields_ if name != "reserved"}
+
+    def reset_stats(self):
+        L.check(L.lib().mrt_reset_stats(self._ctx))
+
+    def intersect_host(self, rays, stride=None):
+        """One MPSRayIntersector-style nearest-hit pass over host rays (structured array or raw bytes)."""
+        rays = np.ascontiguousarray(rays)
+        stride = stride or rays.dtype.itemsize
+        count = rays.nbytes // stride
+        out = np.empty(count, dtype=L.INTERSECTION)
+        L.check(L.lib().mrt_intersect_host(self._ctx, L.ptr(rays), stride, count, L.ptr(out)))
+        return out
+
+    def profile_traversal(self, rays, stride=None):
+        rays = np.ascontiguousarray(rays)
+        stride = stride or rays.dtype.itemsize
+        L.check(L.lib().mrt_profile_traversal(self._ctx, L.ptr(rays), stride, rays.nbytes // stride))
