@@ -88,7 +88,8 @@ typedef struct mrt_stats {
     uint32_t bvh_depth;
     float    bvh_sah_cost;
     float    bvh_build_ms;      /* host wall time of the last SAH build */
-    uint32_t reserved[5];
+    float    last_kernel_ms;    /* device time of the fused kernel alone inside the last mrt_render_frames */
+    uint32_t reserved[4];
 } mrt_stats;
 
 /* Read-only view of a host scene container (arrays in the ABI layouts of mrt_abi.h). */
@@ -164,10 +165,17 @@ int mrt_render_frame_staged(mrt_ctx* ctx, uint32_t frame_index);
  * noise_tiles: host array of (n_frames-1)*frame_stride+1 tiles, tile k belongs to frame
  * first_frame+k and refreshes slot (first_frame+k)%3 before that frame is rendered, exactly as
  * -updateSharedData does (Renderer.mm:485-497).  NULL = no refresh (ANIMATE_NOISE 0).  On return
- * the three slots hold what the reference's would after the last frame.  Asynchronous. */
+ * the three slots hold what the reference's would after the last frame.  noise_tiles may be a host pointer
+ * (pageable: borrowed until the call returns; page-locked: must stay unchanged until mrt_sync) or a device
+ * pointer on the ctx's device (inputs already resident in HBM).  Asynchronous. */
 int mrt_render_frames(mrt_ctx* ctx, uint32_t first_frame, uint32_t n_frames, uint32_t frame_stride,
                       const float* noise_tiles);
 int mrt_sync(mrt_ctx* ctx);
+/* Device-side timing on the ctx stream (CUDA events): record marker `slot` (0..7) now / milliseconds between two
+ * recorded markers (synchronises on the later one).  The reference only has the wall-clock frame time of
+ * Renderer.mm:474-476, 631-637. */
+int mrt_event_record(mrt_ctx* ctx, uint32_t slot);
+int mrt_event_elapsed_ms(mrt_ctx* ctx, uint32_t slot_begin, uint32_t slot_end, float* ms);
 
 /* ---- results / test seams ------------------------------------------------------------------- */
 /* Image read-back (the reference never reads back; -saveCurrentImage is a stub, Renderer.mm:659-662).

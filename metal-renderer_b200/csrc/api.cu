@@ -36,7 +36,9 @@ static const size_t kTileBytes = kTileFloat4 * sizeof(float4);
 struct mrt_ctx {
     mrt_config cfg{};
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, tableCopied = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evK0 = nullptr, evK1 = nullptr, tableCopied = nullptr;
+    cudaEvent_t user[8] = {};
+    bool kernelTimed = false;
     bool timed = false;
     // scene
     DeviceScene S{};
@@ -129,7 +131,8 @@ int mrt_create(const mrt_config* cfg, mrt_ctx** out) {
     c->cfg = def;
     if (c->cfg.bvh_max_leaf == 0) c->cfg.bvh_max_leaf = 4;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CK(cudaEventCreate(&c->ev0)); CK(cudaEventCreate(&c->ev1));
+    CK(cudaEventCreate(&c->ev0)); CK(cudaEventCreate(&c->ev1)); CK(cudaEventCreate(&c->evK0)); CK(cudaEventCreate(&c->evK1));
+    for (auto& e : c->user) CK(cudaEventCreate(&e));
     CK(cudaEventCreateWithFlags(&c->tableCopied, cudaEventDisableTiming));
     CK(cudaMalloc(&c->dCounters, 4 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c->dCounters, 0, 4 * sizeof(unsigned long long), c->stream));
@@ -146,7 +149,8 @@ int mrt_destroy(mrt_ctx* c) {
     free_scene(c); free_sized(c);
     cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters);
     if (c->hFrameTable) cudaFreeHost(c->hFrameTable);
-    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->tableCopied);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->evK0); cudaEventDestroy(c->evK1); cudaEventDestroy(c->tableCopied);
+    for (auto& e : c->user) cudaEventDestroy(e);
     cudaStreamDestroy(c->stream);
     delete c;
     return MRT_OK;
@@ -346,7 +350,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
         for (uint32_t k = 0; k < span; ++k) {
             uint32_t f = first_frame + k;
             if (refresh) CK(cudaMemcpyAsync(c->dNoisePool + (f % 3u) * kTileFloat4, noise_tiles + (size_t)k * MRT_NOISE_TILE_FLOATS, kTileBytes,
-                                            cudaMemcpyHostToDevice, c->stream));
+                                            cudaMemcpyDefault, c->stream));
             if (k % frame_stride == 0) { int rc = mrt_render_frame_staged(c, f); if (rc) return rc; }
         }
     } else {
@@ -355,7 +359,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
         rc = ensure_table(c, n_frames);
         if (rc) return rc;
         if (refresh) CK(cudaMemcpyAsync(c->dNoisePool + MRT_NOISE_SLOTS * kTileFloat4, noise_tiles, (size_t)span * kTileBytes,
-                                        cudaMemcpyHostToDevice, c->stream));
+                                        cudaMemcpyDefault, c->stream));
         CK(cudaEventSynchronize(c->tableCopied));                         // previous batch's table has left the pinned buffer
         uint32_t slotTile[3] = {0, 1, 2};
         uint32_t e = 0;
@@ -370,7 +374,10 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
         p.S = c->S; p.noisePool = c->dNoisePool; p.frames = c->dFrameTable; p.nFrames = n_frames; p.image = c->dImage;
         p.g = c->grid(); p.ownedRows = c->ownedRows(); p.maxPathLength = c->cfg.max_path_length; p.accumMode = c->cfg.accumulate_mode;
         p.counters = c->dCounters;
+        CK(cudaEventRecord(c->evK0, c->stream));
         launch_render_fused(c->stream, p, c->cfg.count_rays != 0);
+        CK(cudaEventRecord(c->evK1, c->stream));
+        c->kernelTimed = true;
         LAUNCHED(c, 1);
         // leave the three slots as the reference's would be after the last frame
         for (uint32_t s = 0; s < 3 && refresh; ++s)
@@ -387,6 +394,20 @@ int mrt_sync(mrt_ctx* c) {
     NEED(c, MRT_E_INVALID, "ctx is NULL");
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaStreamSynchronize(c->stream));
+    return MRT_OK;
+}
+
+int mrt_event_record(mrt_ctx* c, uint32_t slot) {
+    NEED(c && slot < 8, MRT_E_INVALID, "event slot out of range");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaEventRecord(c->user[slot], c->stream));
+    return MRT_OK;
+}
+int mrt_event_elapsed_ms(mrt_ctx* c, uint32_t a, uint32_t b, float* ms) {
+    NEED(c && ms && a < 8 && b < 8, MRT_E_INVALID, "bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaEventSynchronize(c->user[b]));
+    CK(cudaEventElapsedTime(ms, c->user[a], c->user[b]));
     return MRT_OK;
 }
 
@@ -455,6 +476,7 @@ int mrt_get_stats(mrt_ctx* c, mrt_stats* out) {
     CK(cudaMemcpy(h, c->dCounters, sizeof h, cudaMemcpyDeviceToHost));
     c->stats.primary_rays = h[0]; c->stats.shadow_rays = h[1]; c->stats.nodes_visited = h[2]; c->stats.triangles_tested = h[3];
     if (c->timed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->ev0, c->ev1)); c->stats.last_render_ms = ms; }
+    if (c->kernelTimed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->evK0, c->evK1)); c->stats.last_kernel_ms = ms; }
     *out = c->stats;
     return MRT_OK;
 }

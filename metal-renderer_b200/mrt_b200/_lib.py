@@ -48,7 +48,8 @@ class Stats(C.Structure):
     _fields_ = [("primary_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("frames_rendered", C.c_uint64), ("nodes_visited", C.c_uint64), ("triangles_tested", C.c_uint64),
                 ("last_render_ms", C.c_float), ("bvh_nodes", C.c_uint32), ("bvh_depth", C.c_uint32),
-                ("bvh_sah_cost", C.c_float), ("bvh_build_ms", C.c_float), ("reserved", C.c_uint32 * 5)]
+                ("bvh_sah_cost", C.c_float), ("bvh_build_ms", C.c_float), ("last_kernel_ms", C.c_float),
+                ("reserved", C.c_uint32 * 4)]
 
 
 class SceneView(C.Structure):
@@ -88,6 +89,8 @@ SIGNATURES = {
     "mrt_render_frame_staged": (C.c_int, [_P, _U32]),
     "mrt_render_frames": (C.c_int, [_P, _U32, _U32, _U32, _P]),
     "mrt_sync": (C.c_int, [_P]),
+    "mrt_event_record": (C.c_int, [_P, _U32]),
+    "mrt_event_elapsed_ms": (C.c_int, [_P, _U32, _U32, C.POINTER(C.c_float)]),
     "mrt_read_image": (C.c_int, [_P, _P]),
     "mrt_scale_image": (C.c_int, [_P, _F]),
     "mrt_clear_image": (C.c_int, [_P]),

@@ -107,7 +107,7 @@ class Renderer:
             if isinstance(noise_tiles, np.ndarray):
                 assert noise_tiles.dtype == np.float32 and noise_tiles.flags["C_CONTIGUOUS"] and noise_tiles.size >= need
                 p = L.ptr(noise_tiles)
-            else:                                   # raw host address (e.g. a pinned torch tensor's data_ptr())
+            else:                                   # raw host or device address (e.g. a torch tensor's data_ptr())
                 p = C.c_void_p(int(noise_tiles))
         L.check(L.lib().mrt_render_frames(self._ctx, first, n_frames, frame_stride, p))
         if n_frames:
@@ -117,6 +117,14 @@ class Renderer:
 
     def sync(self):
         L.check(L.lib().mrt_sync(self._ctx))
+
+    def event_record(self, slot):
+        L.check(L.lib().mrt_event_record(self._ctx, slot))
+
+    def event_elapsed_ms(self, begin, end):
+        ms = C.c_float()
+        L.check(L.lib().mrt_event_elapsed_ms(self._ctx, begin, end, C.byref(ms)))
+        return ms.value
 
     # ---- results ---------------------------------------------------------------------------------------
     def save_current_image(self, out=None):

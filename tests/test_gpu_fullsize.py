@@ -1,0 +1,66 @@
+"""Full-size GPU checks at BASELINE.json's sizes, through size-independent properties (the oracle would take
+minutes here): fused megakernel == the reference-shaped 34-dispatch sequence bit-for-bit, row shards compose,
+traversal == brute-force definition on sampled rays, ray accounting."""
+import numpy as np
+import pytest
+
+import mrt_b200 as m
+from helpers import bits_equal, random_rays, setup_pair
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_renderer(scene, w, h, L=8, **kw):
+    r = m.Renderer(max_path_length=L, **kw)
+    r.init_raytracing(scene)
+    r.drawable_size_will_change(w, h)
+    init = m.noise_tile(1, 0xFFFFFFFF)
+    for s in range(3):
+        r.update_noise(s, init)
+    return r
+
+
+@pytest.mark.parametrize("name,seed", [("spheres-1m", 3), ("cornell-water", 2)])
+def test_1080p_fused_equals_staged(name, seed):
+    scene = m.Scene.procedural(name, seed)
+    tiles = m.noise_tiles(seed, 0, 3)
+    a = gpu_renderer(scene, 1920, 1080)
+    b = gpu_renderer(scene, 1920, 1080, pipeline=m.PIPELINE_WAVEFRONT)
+    a.draw(3, tiles); b.draw(3, tiles)
+    ia, ib = a.save_current_image(), b.save_current_image()
+    assert bits_equal(ia, ib)
+    sa, sb = a.stats(), b.stats()
+    assert (sa["primary_rays"], sa["shadow_rays"]) == (sb["primary_rays"], sb["shadow_rays"])
+    n = 1920 * 1080 * 3
+    assert n <= sa["primary_rays"] <= 8 * n and 0 < sa["shadow_rays"] <= 7 * n
+    finite = np.isfinite(ia[..., :3])
+    assert finite.mean() > 0.9999 and (ia[..., 3] == 1).all()
+    assert 0.005 < ia[..., :3][finite].mean() < 10
+
+
+def test_1m_triangle_traversal_equals_oracle_on_samples():
+    import oracle as orc
+    scene = m.Scene.procedural("spheres-1m", 3)
+    r = gpu_renderer(scene, 16, 16)
+    o = orc.Oracle(); o.init_raytracing(scene)
+    rays = random_rays(50000, 17)
+    got = r.intersect_host(rays)
+    want = o.intersect_host(rays, bvh=True)
+    assert bits_equal(got, want)
+    few = rays[:64]
+    assert bits_equal(r.intersect_host(few), o.intersect_host(few, bvh=False))          # brute force over 1M triangles
+    st = r.stats()
+    assert st["bvh_depth"] < 62 and st["bvh_nodes"] > 200_000
+
+
+def test_4k_row_shards_compose():
+    scene = m.Scene.procedural("spheres-64k", 4)
+    tiles = m.noise_tiles(4, 0, 2)
+    full = gpu_renderer(scene, 3840, 2160); full.draw(2, tiles)
+    ref = full.save_current_image()
+    acc = np.zeros_like(ref)
+    for g in range(2):
+        r = gpu_renderer(scene, 3840, 2160); r.set_row_shard(g, 2); r.draw(2, tiles)
+        acc[g::2] = r.save_current_image()[g::2]
+        r.close()
+    assert bits_equal(acc, ref)

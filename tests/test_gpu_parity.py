@@ -1,0 +1,177 @@
+"""GPU parity tests: the CUDA path (through the C-ABI of include/mrt.h) against the CPU oracle on the same seeded
+inputs.  Bar: BIT-EXACT for hit IDs, distances, barycentrics, every stage buffer and the accumulated image
+(NaNs compare equal to NaNs).  Sizes here are ones the oracle finishes in seconds."""
+import numpy as np
+import pytest
+
+import mrt_b200 as m
+from helpers import bits_equal, mismatch_report, random_rays, setup_pair
+
+pytestmark = pytest.mark.gpu
+
+
+def assert_bits(a, b, what):
+    assert bits_equal(a, b), f"{what}: {mismatch_report(a, b) if a.dtype.fields else 'arrays differ'}"
+
+
+def test_raygen_buffer_bits():
+    scene = m.Scene.procedural("cornell", 0)
+    for (w, h) in ((256, 256), (101, 37), (2, 2)):
+        r, o = setup_pair(scene, w, h)
+        r.raygen(0); o.raygen(0)
+        assert_bits(r.read_buffer(m.BUF_RAYS), o.read_buffer(0), f"rays {w}x{h}")
+
+
+@pytest.mark.parametrize("name,n", [("cornell", 20000), ("cornell-water", 20000), ("spheres-64k", 20000), ("many-lights", 8000)])
+def test_intersector_matches_oracle(name, n):
+    scene = m.Scene.procedural(name, 3)
+    r, o = setup_pair(scene, 8, 8)
+    rays = random_rays(n, 11)
+    rays["maxDistance"][::17] = -1.0                       # skipped rays
+    rays["maxDistance"][1::19] = 0.7                       # finite range
+    rays["minDistance"][2::23] = 0.3
+    got = r.intersect_host(rays)
+    want = o.intersect_host(rays, bvh=(name != "cornell"))  # brute force defines the answer on the small scene
+    assert_bits(got, want, name)
+    # strided records (80-byte Ray layout, MPS rayStride) give the same answer
+    wide = random_rays(n, 11, dtype=m.RAY)
+    for f in ("maxDistance", "minDistance"):
+        wide[f] = rays[f]
+    assert_bits(r.intersect_host(wide), want, name + " stride 80")
+
+
+def test_every_stage_buffer_matches_oracle():
+    scene = m.Scene.procedural("cornell-water", 0)         # diffuse + plastic + mirror
+    w, h, L = 96, 64, 5
+    r, o = setup_pair(scene, w, h, max_path_length=L)
+    tiles = m.noise_tiles(21, 0, 3)
+    for f in range(3):
+        r.update_noise(f % 3, tiles[f]); o.update_noise(f % 3, tiles[f])
+        r.raygen(f); o.raygen(f)
+        assert_bits(r.read_buffer(m.BUF_RAYS), o.read_buffer(0), f"f{f} raygen")
+        for i in range(L):
+            r.intersect(m.BUF_RAYS); o.intersect(0)
+            assert_bits(r.read_buffer(m.BUF_INTERSECTIONS), o.read_buffer(2), f"f{f} i{i} primary hits")
+            r.shade(f, i); o.shade(f, i)
+            assert_bits(r.read_buffer(m.BUF_RAYS), o.read_buffer(0), f"f{f} i{i} shade rays")
+            assert_bits(r.read_buffer(m.BUF_LIGHT_RAYS), o.read_buffer(1), f"f{f} i{i} light rays")
+            r.intersect(m.BUF_LIGHT_RAYS); o.intersect(1)
+            assert_bits(r.read_buffer(m.BUF_INTERSECTIONS), o.read_buffer(2), f"f{f} i{i} shadow hits")
+            r.shadow_resolve(); o.shadow_resolve()
+            assert_bits(r.read_buffer(m.BUF_RAYS), o.read_buffer(0), f"f{f} i{i} resolve")
+        r.accumulate(f); o.accumulate(f)
+        assert_bits(r.read_buffer(m.BUF_IMAGE), o.read_buffer(3), f"f{f} image")
+
+
+def render_both(scene, w, h, frames, L, seed, pipeline=m.PIPELINE_AUTO, **kw):
+    r, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(pipeline=pipeline))
+    tiles = m.noise_tiles(seed, 0, frames)
+    r.draw(frames, tiles); o.draw(frames, tiles)
+    return r, o
+
+
+def test_config1_cornell_256_16spp_depth4_bit_exact():
+    """BASELINE.json configs[0]: procedural Cornell 256x256, 16 spp, max depth 4."""
+    scene = m.Scene.procedural("cornell", 0)
+    r, o = render_both(scene, 256, 256, 16, 4, seed=1)
+    gi, oi = r.save_current_image(), o.save_current_image()
+    assert_bits(gi, oi, "image")
+    st, oc = r.stats(), o.counts()
+    assert (st["primary_rays"], st["shadow_rays"]) == (oc["primary_rays"], oc["shadow_rays"])
+    assert st["kernel_launches"] == 1
+    # primary-hit triangle IDs: bit-equal on 100% of pixels
+    r2, o2 = setup_pair(scene, 256, 256)
+    r2.raygen(0); o2.raygen(0); r2.intersect(); o2.intersect()
+    assert np.array_equal(r2.read_buffer(m.BUF_INTERSECTIONS)["triangleIndex"], o2.read_buffer(2)["triangleIndex"])
+
+
+@pytest.mark.parametrize("name,w,h,frames,L", [("cornell-water", 160, 90, 6, 8), ("spheres-64k", 128, 72, 4, 8),
+                                                ("many-lights", 96, 54, 4, 8), ("white-box", 64, 64, 5, 3)])
+def test_fused_render_bit_exact(name, w, h, frames, L):
+    scene = m.Scene.procedural(name, 5)
+    r, o = render_both(scene, w, h, frames, L, seed=7)
+    assert_bits(r.save_current_image(), o.save_current_image(), name)
+    st, oc = r.stats(), o.counts()
+    assert (st["primary_rays"], st["shadow_rays"]) == (oc["primary_rays"], oc["shadow_rays"])
+
+
+def test_wavefront_pipeline_and_continuation_bit_exact():
+    scene = m.Scene.procedural("cornell-water", 0)
+    w, h, L = 120, 68, 6
+    tiles = m.noise_tiles(3, 0, 7)
+    a, o = setup_pair(scene, w, h, max_path_length=L)                                   # fused, in two batches
+    b, _ = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(pipeline=m.PIPELINE_WAVEFRONT))
+    a.draw(3, tiles[:3]); a.draw(4, tiles[3:])                                           # slots carry over between calls
+    b.draw(7, tiles)
+    o.draw(7, tiles)
+    want = o.save_current_image()
+    assert_bits(a.save_current_image(), want, "fused 3+4")
+    assert_bits(b.save_current_image(), want, "wavefront")
+    assert b.stats()["kernel_launches"] == 7 * (2 + 4 * L)
+
+
+def test_noise_zero_produces_identical_nans():
+    # noise.w == 0 makes bsdf/pdf = 0/0 (Shaders.metal:209): the NaNs must appear in the same pixels
+    scene = m.Scene.procedural("cornell", 0)
+    tiles = m.noise_tiles(2, 0, 3).copy()
+    tiles[:, 3::4][:, ::5] = 0.0
+    tiles[:, 2::4][:, ::7] = 0.0
+    r, o = setup_pair(scene, 64, 64, max_path_length=4)
+    r.draw(3, tiles); o.draw(3, tiles)
+    gi, oi = r.save_current_image(), o.save_current_image()
+    assert_bits(gi, oi, "image with NaNs")
+
+
+def test_accumulate_modes_and_row_shards():
+    scene = m.Scene.procedural("cornell", 0)
+    w, h, L = 64, 48, 4
+    tiles = m.noise_tiles(8, 0, 4)
+    for mode in (m.ACCUM_SUM, m.ACCUM_REPLACE):
+        r, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(accumulate_mode=mode))
+        o.set_accumulate_mode(mode)
+        r.draw(4, tiles); o.draw(4, tiles)
+        assert_bits(r.save_current_image(), o.save_current_image(), f"mode {mode}")
+    # row sharding: 3 shards compose to the unsharded image bit-for-bit; strided frames match the oracle
+    full, o = setup_pair(scene, w, h, max_path_length=L)
+    full.draw(4, tiles)
+    ref = full.save_current_image()
+    acc = np.zeros_like(ref)
+    for g in range(3):
+        r, _ = setup_pair(scene, w, h, max_path_length=L)
+        r.set_row_shard(g, 3)
+        r.draw(4, tiles)
+        acc[g::3] = r.save_current_image()[g::3]
+    assert_bits(acc, ref, "row shards")
+    r, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(accumulate_mode=m.ACCUM_SUM))
+    o.set_accumulate_mode(m.ACCUM_SUM)
+    r.draw(2, tiles, first_frame=1, frame_stride=2); o.draw(2, tiles, first_frame=1, frame_stride=2)   # frames 1, 3
+    assert_bits(r.save_current_image(), o.save_current_image(), "strided frames")
+
+
+def test_error_paths():
+    r = m.Renderer()
+    with pytest.raises(m.MrtError) as e:
+        r.raygen(0)
+    assert e.value.code == -5                                  # MRT_E_STATE: no scene
+    scene = m.Scene.procedural("cornell", 0)
+    r.init_raytracing(scene)
+    with pytest.raises(m.MrtError):
+        r.drawable_size_will_change(1, 10)                     # raygen divides by size-1
+    bad = m.Scene.procedural("cornell", 0)
+    bad.indices[5] = 10_000
+    with pytest.raises(m.MrtError) as e:
+        r.init_raytracing(bad)
+    assert e.value.code == -1
+    with pytest.raises(m.MrtError):
+        m.Renderer(max_path_length=0)
+
+
+def test_empty_and_single_triangle_scene():
+    import oracle as orc
+    scene = m.Scene.procedural("cornell", 0)
+    one = m.Scene(scene.vertices, scene.indices[:3], scene.references[:1], scene.materials, scene.lights[-1:], 0)
+    r, o = setup_pair(one, 32, 32)
+    rays = random_rays(2000, 5)
+    assert_bits(r.intersect_host(rays), o.intersect_host(rays, bvh=False), "one triangle")
+    r.draw(2, m.noise_tiles(1, 0, 2)); o.draw(2, m.noise_tiles(1, 0, 2))
+    assert_bits(r.save_current_image(), o.save_current_image(), "one triangle image")
