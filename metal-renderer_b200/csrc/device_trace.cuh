@@ -45,9 +45,14 @@ __device__ __forceinline__ HitRec trace_nearest(const float4* __restrict__ nodes
                                                 f3 o, f3 d, float tmin, float tmax,
                                                 unsigned long long* nodesVisited, unsigned long long* trisTested) {
     HitRec best; best.t = tmax; best.tri = MRT_NO_HIT; best.u = 0.0f; best.v = 0.0f;
-    // slab test in fma form: t = plane * (1/d) - o * (1/d).  Not bit-matched with anything — only conservative:
-    // NaNs (0 * inf) fall out of fminf/fmaxf, and the boxes carry the builder's padding.
-    const float idx = __fdiv_rn(1.0f, d.x), idy = __fdiv_rn(1.0f, d.y), idz = __fdiv_rn(1.0f, d.z);
+    // slab test in fma form: t = plane * (1/d) - o * (1/d).  Not bit-matched with anything — only conservative
+    // (the boxes carry the builder's padding).  Direction components are kept away from zero FOR THE BOX TEST
+    // ONLY, so 1/d stays finite: with an infinite reciprocal plane*inf - o*inf is NaN for one of the two planes
+    // and fminf/fmaxf would then turn an axis-parallel ray inside the slab into a miss.
+    const float tiny = 1e-30f;
+    const float idx = __fdiv_rn(1.0f, fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x);
+    const float idy = __fdiv_rn(1.0f, fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y);
+    const float idz = __fdiv_rn(1.0f, fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
     const float ox = o.x * idx, oy = o.y * idy, oz = o.z * idz;
     int stack[MRT_STACK_DEPTH];
     int sp = 0;

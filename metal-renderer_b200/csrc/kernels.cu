@@ -6,6 +6,7 @@
 //   * the fused megakernel: one launch renders whole frames with the path state in registers, lanes that finish
 //     a sample start the next one at once, and primary and shadow rays share one traversal site.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false (see device_math.cuh for why).
+#include <cstdlib>
 #include "kernels.h"
 #include "device_trace.cuh"
 
@@ -135,8 +136,8 @@ __global__ void __launch_bounds__(256) k_scale_image(float4* __restrict__ image,
 // sequence of float operations per pixel is exactly the stage sequence of Renderer.mm:504-584.
 enum { PH_GEN = 0, PH_PRIMARY = 1, PH_SHADOW = 2 };
 
-template <bool COUNT>
-__global__ void __launch_bounds__(256, 2) k_render_fused(RenderParams P) {
+template <bool COUNT, int MINB>
+__global__ void __launch_bounds__(256, MINB) k_render_fused(RenderParams P) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t tilesX = (P.g.W + 7u) >> 3;
@@ -252,15 +253,17 @@ void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays) 
     uint32_t warps = tilesX * tilesY;
     if (warps == 0 || p.nFrames == 0) return;
     uint32_t blocks = (warps + 7u) / 8u;
-    if (countRays) k_render_fused<true><<<blocks, 256, 0, s>>>(p);
-    else k_render_fused<false><<<blocks, 256, 0, s>>>(p);
+    static const int minb = [] { const char* e = getenv("MRT_FUSED_MINBLOCKS"); int v = e ? atoi(e) : 2; return v; }();
+    if (minb >= 4)      { if (countRays) k_render_fused<true, 4><<<blocks, 256, 0, s>>>(p); else k_render_fused<false, 4><<<blocks, 256, 0, s>>>(p); }
+    else if (minb == 3) { if (countRays) k_render_fused<true, 3><<<blocks, 256, 0, s>>>(p); else k_render_fused<false, 3><<<blocks, 256, 0, s>>>(p); }
+    else                { if (countRays) k_render_fused<true, 2><<<blocks, 256, 0, s>>>(p); else k_render_fused<false, 2><<<blocks, 256, 0, s>>>(p); }
 }
 int fused_kernel_info(int* regs, int* maxBlocksPerSM) {
     cudaFuncAttributes a;
-    cudaError_t e = cudaFuncGetAttributes(&a, k_render_fused<true>);
+    cudaError_t e = cudaFuncGetAttributes(&a, k_render_fused<true, 2>);
     if (e != cudaSuccess) return (int)e;
     *regs = a.numRegs;
-    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true>, 256, 0);
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true, 2>, 256, 0);
 }
 
 }  // namespace mrt

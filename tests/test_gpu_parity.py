@@ -30,6 +30,10 @@ def test_intersector_matches_oracle(name, n):
     rays["maxDistance"][::17] = -1.0                       # skipped rays
     rays["maxDistance"][1::19] = 0.7                       # finite range
     rays["minDistance"][2::23] = 0.3
+    # axis-parallel directions (exact zero components): 1/d is infinite — the slab test must stay conservative
+    axes = np.array([[0, 0, -1], [0, -1, 0], [1, 0, 0], [0, 0.6, -0.8], [-0.6, 0, 0.8], [0.8, -0.6, 0], [-0.0, 1, 0]], np.float32)
+    rays["direction"][3::29] = axes[np.arange(len(rays["direction"][3::29])) % len(axes)]
+    rays["origin"][3::58] = np.round(rays["origin"][3::58] * 4) / 4     # some origins exactly on wall / box planes
     got = r.intersect_host(rays)
     want = o.intersect_host(rays, bvh=(name != "cornell"))  # brute force defines the answer on the small scene
     assert_bits(got, want, name)
