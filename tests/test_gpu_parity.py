@@ -39,7 +39,7 @@ def test_intersector_matches_oracle(name, n):
     assert_bits(got, want, name)
     # strided records (80-byte Ray layout, MPS rayStride) give the same answer
     wide = random_rays(n, 11, dtype=m.RAY)
-    for f in ("maxDistance", "minDistance"):
+    for f in ("origin", "direction", "maxDistance", "minDistance"):
         wide[f] = rays[f]
     assert_bits(r.intersect_host(wide), want, name + " stride 80")
 
