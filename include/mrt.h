@@ -39,8 +39,10 @@ enum {
 /* Traversal / pipeline variant used by mrt_render_frames. */
 enum {
     MRT_PIPELINE_AUTO = 0,
-    MRT_PIPELINE_MEGAKERNEL = 1,   /* one persistent fused kernel, ray state in registers */
-    MRT_PIPELINE_WAVEFRONT = 2     /* staged kernels with warp-ballot compaction of live rays */
+    MRT_PIPELINE_MEGAKERNEL = 1,   /* one fused kernel per batch of frames, path state in registers */
+    MRT_PIPELINE_WAVEFRONT = 2,    /* queue-compacted waves: persistent dynamic-fetch trace kernel + shade kernel, SoA
+                                      path state in HBM, warp-ballot compaction of live rays (AUTO selects this) */
+    MRT_PIPELINE_STAGED = 3        /* the reference's own 2 + 4*L dispatches per frame over the ABI buffers */
 };
 
 /* How mrt_accumulate / mrt_render_frames fold a frame into the image. */

@@ -53,6 +53,10 @@ struct mrt_ctx {
     float4* dNoisePool = nullptr; size_t poolTiles = 0;
     uint4* dFrameTable = nullptr; FrameEntry* hFrameTable = nullptr; size_t tableCap = 0;
     unsigned long long* dCounters = nullptr;     // primary, shadow, nodes, tris
+    unsigned int* dHead = nullptr;               // work counter of the persistent intersector (staged entry points)
+    void* dTriSlot = nullptr;                    // original triangle index -> leaf-order record
+    WfBuffers wf{};                              // wavefront path state + queues (sized by mrt_resize)
+    void* wfArena = nullptr;
     mrt_stats stats{};
 
     Grid2D grid() const { Grid2D g; g.W = W; g.H = H; g.rowFirst = rowFirst; g.rowStride = rowStride; return g; }
@@ -61,12 +65,17 @@ struct mrt_ctx {
 
 static void free_scene(mrt_ctx* c) {
     cudaFree(c->dNodes); cudaFree(c->dTris); cudaFree(c->dShade); cudaFree(c->dMats); cudaFree(c->dLights); cudaFree(c->dCdf);
-    c->dNodes = c->dTris = c->dShade = c->dMats = c->dLights = c->dCdf = nullptr;
+    cudaFree(c->dTriSlot);
+    c->dNodes = c->dTris = c->dShade = c->dMats = c->dLights = c->dCdf = c->dTriSlot = nullptr;
+    c->wf.triSlot = nullptr;
     c->haveScene = false;
 }
 static void free_sized(mrt_ctx* c) {
-    cudaFree(c->dRays); cudaFree(c->dLightRays); cudaFree(c->dIsects); cudaFree(c->dImage);
-    c->dRays = nullptr; c->dLightRays = nullptr; c->dIsects = nullptr; c->dImage = nullptr;
+    cudaFree(c->dRays); cudaFree(c->dLightRays); cudaFree(c->dIsects); cudaFree(c->dImage); cudaFree(c->wfArena);
+    c->dRays = nullptr; c->dLightRays = nullptr; c->dIsects = nullptr; c->dImage = nullptr; c->wfArena = nullptr;
+    const uint32_t* triSlot = c->wf.triSlot;
+    c->wf = WfBuffers{};
+    c->wf.triSlot = triSlot;
 }
 static int ensure_pool(mrt_ctx* c, size_t tiles) {
     if (tiles <= c->poolTiles) return MRT_OK;
@@ -120,7 +129,7 @@ int mrt_create(const mrt_config* cfg, mrt_ctx** out) {
     if (cfg) { NEED(cfg->struct_size == sizeof(mrt_config), MRT_E_INVALID, "mrt_create: struct_size %u != %zu", cfg->struct_size, sizeof(mrt_config)); def = *cfg; }
     NEED(def.max_path_length >= 1 && def.max_path_length <= 64, MRT_E_INVALID, "max_path_length must be in 1..64");
     NEED(def.accumulate_mode <= MRT_ACCUM_REPLACE, MRT_E_INVALID, "bad accumulate_mode");
-    NEED(def.pipeline <= MRT_PIPELINE_WAVEFRONT, MRT_E_INVALID, "bad pipeline");
+    NEED(def.pipeline <= MRT_PIPELINE_STAGED, MRT_E_INVALID, "bad pipeline");
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0) return fail(MRT_E_CUDA, "no CUDA device (%s); this library has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "count 0");
@@ -136,6 +145,7 @@ int mrt_create(const mrt_config* cfg, mrt_ctx** out) {
     CK(cudaEventCreateWithFlags(&c->tableCopied, cudaEventDisableTiming));
     CK(cudaMalloc(&c->dCounters, 4 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(c->dCounters, 0, 4 * sizeof(unsigned long long), c->stream));
+    CK(cudaMalloc(&c->dHead, sizeof(unsigned int)));
     int rc = ensure_pool(c, MRT_NOISE_SLOTS + 16);
     if (rc) { delete c; return rc; }
     *out = c;
@@ -147,7 +157,7 @@ int mrt_destroy(mrt_ctx* c) {
     cudaSetDevice(c->cfg.device);
     cudaStreamSynchronize(c->stream);
     free_scene(c); free_sized(c);
-    cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters);
+    cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters); cudaFree(c->dHead);
     if (c->hFrameTable) cudaFreeHost(c->hFrameTable);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->evK0); cudaEventDestroy(c->evK1); cudaEventDestroy(c->tableCopied);
     for (auto& e : c->user) cudaEventDestroy(e);
@@ -211,6 +221,10 @@ int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count,
     CK(upload(&c->dMats, mats.data(), mats.size() * 4));
     CK(upload(&c->dLights, lts.data(), lts.size() * 4));
     CK(upload(&c->dCdf, cdf.data(), cdf.size() * 4));
+    std::vector<uint32_t> triSlot(std::max(1u, triangle_count), 0u);
+    for (size_t k = 0; k < bvh.tris.size(); ++k) triSlot[bvh.tris[k].index] = (uint32_t)k;
+    CK(upload(&c->dTriSlot, triSlot.data(), triSlot.size() * 4));
+    c->wf.triSlot = (const uint32_t*)c->dTriSlot;
     c->S.nodes = (const float4*)c->dNodes; c->S.tris = (const float4*)c->dTris; c->S.shadeTris = (const float4*)c->dShade;
     c->S.materials = (const float4*)c->dMats; c->S.lights = (const float4*)c->dLights; c->S.lightCdf = (const float*)c->dCdf;
     c->S.lightCount = light_count; c->S.triangleCount = triangle_count;
@@ -243,6 +257,22 @@ int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
     CK(cudaMemsetAsync(c->dIsects, 0, n * sizeof(mrt_intersection), c->stream));
     CK(cudaMemsetAsync(c->dImage, 0, n * sizeof(float4), c->stream));
     c->W = width; c->H = height;
+    {   // wavefront path state: one slot per pixel of an 8x4-tiled grid, SoA float4 arrays + two queue pairs
+        const size_t slots = (size_t)((width + 7u) / 8u) * ((height + 3u) / 4u) * 32u;
+        const size_t f4 = slots * sizeof(float4), u4 = slots * sizeof(uint32_t);
+        const size_t total = 7 * f4 + 6 * u4 + 64;
+        CK(cudaMalloc(&c->wfArena, total));
+        CK(cudaMemsetAsync(c->wfArena, 0, total, c->stream));
+        char* p = static_cast<char*>(c->wfArena);
+        auto take4 = [&]() { float4* r = reinterpret_cast<float4*>(p); p += f4; return r; };
+        auto takeU = [&]() { uint32_t* r = reinterpret_cast<uint32_t*>(p); p += u4; return r; };
+        c->wf.P0 = take4(); c->wf.P1 = take4(); c->wf.P2 = take4(); c->wf.P3 = take4(); c->wf.H = take4();
+        c->wf.S0 = take4(); c->wf.S1 = take4();
+        c->wf.visible = takeU(); c->wf.cursor = takeU();
+        c->wf.queueExt[0] = takeU(); c->wf.queueExt[1] = takeU(); c->wf.queueShadow[0] = takeU(); c->wf.queueShadow[1] = takeU();
+        c->wf.counts = reinterpret_cast<unsigned int*>(p); c->wf.heads = c->wf.counts + 4;
+        c->wf.slots = (uint32_t)slots;
+    }
     return MRT_OK;
 }
 
@@ -266,7 +296,7 @@ int mrt_set_accumulate_mode(mrt_ctx* c, uint32_t mode) {
     return MRT_OK;
 }
 int mrt_set_pipeline(mrt_ctx* c, uint32_t pipeline) {
-    NEED(c && pipeline <= MRT_PIPELINE_WAVEFRONT, MRT_E_INVALID, "bad pipeline");
+    NEED(c && pipeline <= MRT_PIPELINE_STAGED, MRT_E_INVALID, "bad pipeline");
     c->cfg.pipeline = pipeline;
     return MRT_OK;
 }
@@ -295,7 +325,8 @@ int mrt_intersect(mrt_ctx* c, uint32_t which) {
     const void* rays = which == MRT_BUF_RAYS ? (const void*)c->dRays : (const void*)c->dLightRays;
     uint32_t stride = which == MRT_BUF_RAYS ? sizeof(mrt_ray) : sizeof(mrt_light_sampling_ray);  // setRayStride, Renderer.mm:519,545
     unsigned long long* live = c->cfg.count_rays ? c->dCounters + (which == MRT_BUF_RAYS ? 0 : 1) : nullptr;
-    launch_intersect(c->stream, c->S, rays, stride, c->W * c->H, c->dIsects, c->grid(), true, live, nullptr);
+    CK(cudaMemsetAsync(c->dHead, 0, sizeof(unsigned int), c->stream));
+    launch_intersect_persistent(c->stream, c->S, rays, stride, c->W * c->H, c->dIsects, c->grid(), true, live, c->dHead);
     LAUNCHED(c, 1);
     return MRT_OK;
 }
@@ -345,7 +376,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
     const bool refresh = noise_tiles != nullptr && c->cfg.animate_noise;
     CK(cudaEventRecord(c->ev0, c->stream));
 
-    if (c->cfg.pipeline == MRT_PIPELINE_WAVEFRONT) {
+    if (c->cfg.pipeline == MRT_PIPELINE_STAGED) {
         // the reference's own shape: per frame refresh slot f%3 (Renderer.mm:492-496), then 2 + 4*L dispatches
         for (uint32_t k = 0; k < span; ++k) {
             uint32_t f = first_frame + k;
@@ -373,12 +404,29 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
         RenderParams p;
         p.S = c->S; p.noisePool = c->dNoisePool; p.frames = c->dFrameTable; p.nFrames = n_frames; p.image = c->dImage;
         p.g = c->grid(); p.ownedRows = c->ownedRows(); p.maxPathLength = c->cfg.max_path_length; p.accumMode = c->cfg.accumulate_mode;
-        p.counters = c->dCounters;
+        p.counters = c->cfg.count_rays ? c->dCounters : nullptr;
         CK(cudaEventRecord(c->evK0, c->stream));
-        launch_render_fused(c->stream, p, c->cfg.count_rays != 0);
+        if (c->cfg.pipeline == MRT_PIPELINE_MEGAKERNEL) {
+            p.counters = c->dCounters;
+            launch_render_fused(c->stream, p, c->cfg.count_rays != 0);
+            LAUNCHED(c, 1);
+        } else {
+            // queue-compacted wavefront: init wave, then at most n_frames * L {trace, shade} waves (a slot needs one
+            // trace per path segment); waves that find both queues empty return at once
+            WfBuffers b = c->wf;
+            b.slots = ((c->W + 7u) / 8u) * ((p.ownedRows + 3u) / 4u) * 32u;
+            CK(cudaMemsetAsync(b.counts, 0, 6 * sizeof(unsigned int), c->stream));
+            const bool count = c->cfg.count_rays != 0;
+            launch_wf_shade(c->stream, p, b, 0, true, count);
+            const uint64_t waves = (uint64_t)n_frames * c->cfg.max_path_length;
+            for (uint64_t w = 0; w < waves; ++w) {
+                launch_wf_trace(c->stream, p, b, (uint32_t)(w & 1u));
+                launch_wf_shade(c->stream, p, b, (uint32_t)(w & 1u), false, count);
+            }
+            LAUNCHED(c, 1 + 2 * waves);
+        }
         CK(cudaEventRecord(c->evK1, c->stream));
         c->kernelTimed = true;
-        LAUNCHED(c, 1);
         // leave the three slots as the reference's would be after the last frame
         for (uint32_t s = 0; s < 3 && refresh; ++s)
             if (slotTile[s] != s) CK(cudaMemcpyAsync(c->dNoisePool + s * kTileFloat4, c->dNoisePool + slotTile[s] * kTileFloat4, kTileBytes,

@@ -101,4 +101,116 @@ done:
     return best;
 }
 
+// ---- persistent warp-level traversal with dynamic ray fetch ---------------------------------------------------
+// The per-ray routine above makes a warp wait for its slowest ray (ncu on the 1M-triangle scene: 5.4 of 32 lanes
+// active inside the node loop).  Here a warp owns 32 traversal contexts and keeps pulling work items from a
+// global counter: whenever fewer than `refillBelow` lanes still hold a ray, the idle lanes fetch new ones, so
+// the node/leaf loop runs with most lanes busy regardless of how ray lengths are distributed.  Per ray the
+// arithmetic — and therefore the answer, min over all triangles of (t, index) — is that of trace_nearest.
+//
+// IO policy:
+//   bool load(uint32_t item, TraceJob& job)   fetch work item; false = nothing to traverse (policy already
+//                                             stored the result, e.g. a skipped ray)
+//   void store(uint32_t tag, uint32_t target, const HitRec& best)      target == MRT_NO_HIT for nearest-hit jobs
+// A job is either NEAREST (full record) or ANYHIT: best starts as (tTarget, target) and the ray ends at the first
+// triangle that beats it lexicographically, i.e. exactly when the nearest hit would not be the target.
+struct TraceJob {
+    f3 o, d;
+    float tmin, tmax;
+    uint32_t target;        // MRT_NO_HIT for nearest-hit jobs
+    uint32_t tag;           // handed back to store() (ray index / path slot)
+};
+#define MRT_TRACE_DONE ((int)0x80000000)
+
+template <class IO>
+__device__ __forceinline__ void trace_persistent(const float4* __restrict__ nodes, const float4* __restrict__ tris,
+                                                 uint32_t total, unsigned int* head, uint32_t refillBelow, IO& io) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const float tiny = 1e-30f;
+    bool alive = false, exhausted = (total == 0);
+    uint32_t tag = 0, target = MRT_NO_HIT;
+    f3 o = mk3(0.f, 0.f, 0.f), d = o;
+    float idx = 0.f, idy = 0.f, idz = 0.f, ox = 0.f, oy = 0.f, oz = 0.f, tmin = 0.f, tmax = 0.f;
+    HitRec best; best.t = 0.f; best.tri = MRT_NO_HIT; best.u = best.v = 0.f;
+    int stack[MRT_STACK_DEPTH];
+    int sp = 0, cur = MRT_TRACE_DONE;
+
+    for (;;) {
+        // ---- refill idle lanes until enough of the warp is busy (or the queue is empty) ----
+        unsigned am;
+        for (;;) {
+            am = __ballot_sync(0xffffffffu, alive);
+            if (exhausted || __popc(am) >= (int)refillBelow) break;
+            unsigned need = ~am;
+            uint32_t n = __popc(need), base = 0;
+            int leader = __ffs(need) - 1;
+            if ((int)lane == leader) base = atomicAdd(head, n);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!alive) {
+                uint32_t it = base + __popc(need & ((1u << lane) - 1u));
+                if (it < total) {
+                    TraceJob job;
+                    if (io.load(it, job)) {
+                        tag = job.tag; o = job.o; d = job.d; tmin = job.tmin; tmax = job.tmax; target = job.target;
+                        idx = __fdiv_rn(1.0f, fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x);
+                        idy = __fdiv_rn(1.0f, fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y);
+                        idz = __fdiv_rn(1.0f, fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
+                        ox = o.x * idx; oy = o.y * idy; oz = o.z * idz;
+                        best.t = tmax; best.tri = target; best.u = 0.0f; best.v = 0.0f;
+                        stack[0] = MRT_TRACE_DONE; sp = 1; cur = 0;
+                        alive = true;
+                    }
+                }
+            }
+            exhausted = base + n >= total;
+        }
+        if (am == 0) break;                               // queue empty and every lane idle
+
+        // ---- traverse: each round takes a lane to its next leaf and through it ----
+        for (;;) {
+            if (alive) {
+                while (cur >= 0) {
+                    const float4* np = nodes + 4 * (size_t)cur;
+                    float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+                    float c0x0 = __fmaf_rn(n0.x, idx, -ox), c0x1 = __fmaf_rn(n0.y, idx, -ox);
+                    float c0y0 = __fmaf_rn(n0.z, idy, -oy), c0y1 = __fmaf_rn(n0.w, idy, -oy);
+                    float c0z0 = __fmaf_rn(n2.x, idz, -oz), c0z1 = __fmaf_rn(n2.y, idz, -oz);
+                    float c1x0 = __fmaf_rn(n1.x, idx, -ox), c1x1 = __fmaf_rn(n1.y, idx, -ox);
+                    float c1y0 = __fmaf_rn(n1.z, idy, -oy), c1y1 = __fmaf_rn(n1.w, idy, -oy);
+                    float c1z0 = __fmaf_rn(n2.z, idz, -oz), c1z1 = __fmaf_rn(n2.w, idz, -oz);
+                    float tn0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
+                    float tf0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), best.t));
+                    float tn1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
+                    float tf1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), best.t));
+                    bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+                    int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+                    if (h0 && h1) {
+                        if (tn1 < tn0) { int t = c0; c0 = c1; c1 = t; }
+                        stack[sp++] = c1;
+                        cur = c0;
+                    } else if (h0 || h1) {
+                        cur = h0 ? c0 : c1;
+                    } else {
+                        cur = stack[--sp];
+                    }
+                }
+                if (cur != MRT_TRACE_DONE) {
+                    uint32_t code = ~uint32_t(cur);
+                    uint32_t first = code >> 3, count = code & 7u;
+                    for (uint32_t k = 0; k < count; ++k) triangle_test(tris, first + k, o, d, tmin, tmax, best);
+                    // an any-hit job is decided as soon as something beats (tTarget, target)
+                    cur = (target != MRT_NO_HIT && best.tri != target) ? MRT_TRACE_DONE : stack[--sp];
+                }
+                if (cur == MRT_TRACE_DONE) {
+                    if (best.tri == MRT_NO_HIT) best.t = -1.0f;
+                    io.store(tag, target, best);
+                    alive = false;
+                }
+            }
+            unsigned a2 = __ballot_sync(0xffffffffu, alive);
+            if (a2 == 0 || (!exhausted && __popc(a2) < (int)refillBelow)) break;
+        }
+    }
+}
+
 }  // namespace mrt

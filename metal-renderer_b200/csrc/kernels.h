@@ -37,6 +37,36 @@ void launch_shadow_resolve(cudaStream_t s, const mrt_intersection* isects, mrt_r
 void launch_accumulate(cudaStream_t s, float4* image, const mrt_ray* rays, uint32_t frameIndex, uint32_t mode, Grid2D g);
 void launch_scale_image(cudaStream_t s, float4* image, float scale, uint32_t count);
 
+// persistent (dynamic-fetch) form of launch_intersect: same arguments and results; `head` = zeroed work counter
+void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const void* rays, uint32_t strideBytes, uint32_t count,
+                                 mrt_intersection* out, Grid2D g, bool useGrid, unsigned long long* liveCounter,
+                                 unsigned int* head);
+
+// ---- queue-compacted wavefront: path state as SoA in HBM, one slot per owned pixel ------------------------------
+// A wave = k_wf_trace (persistent; extension rays -> nearest hit, light-sampling rays -> visibility) followed by
+// k_wf_shade (resolve + intersectionHandler + accumulate/regenerate), which compacts the next wave's two queues
+// with warp ballots.  Parity p = wave & 1 selects the queue pair a wave consumes; the other pair is being filled.
+struct WfBuffers {
+    float4* P0;          // origin.xyz, bsdf pdf            |
+    float4* P1;          // direction.xyz, prev-diffuse flag | = the live fields of the reference's Ray
+    float4* P2;          // throughput.xyz, bounce           |   (Raytracing.h:54-69)
+    float4* P3;          // radiance.xyz, ior                |
+    float4* H;           // nearest hit of the extension ray: t, triangle, u, v   (Intersection, Raytracing.h:85-90)
+    float4* S0;          // light-sampling ray: direction.xyz, distance of the target along it
+    float4* S1;          //                     throughput.xyz, targetIndex      (LightSamplingRay, Raytracing.h:71-83)
+    uint32_t* visible;   // 1 iff the light-sampling ray's nearest hit is its target (Shaders.metal:225)
+    uint32_t* cursor;    // bits 0..30: index into the frame table of the sample in flight; bit 31: light ray pending
+    uint32_t* queueExt[2];
+    uint32_t* queueShadow[2];
+    unsigned int* counts;    // [parity][0 ext, 1 shadow]
+    unsigned int* heads;     // [parity] work counter of the persistent trace kernel
+    const uint32_t* triSlot; // original triangle index -> leaf-order record (bvh.h)
+    uint32_t slots;          // tilesX * tilesY * 32
+};
+void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays);
+void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave);
+int wf_kernel_info(int* traceRegs, int* traceBlocksPerSM, int* shadeRegs);
+
 // fused megakernel: whole frames, ray state in registers
 void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays);
 int fused_kernel_info(int* regs, int* maxBlocksPerSM);

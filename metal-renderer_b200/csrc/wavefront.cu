@@ -1,0 +1,272 @@
+// wavefront.cu — queue-compacted wavefront form of the per-pixel pipeline, and the persistent intersector.
+//
+// Same arithmetic as the stage kernels / megakernel of kernels.cu (device_shading.cuh, device_trace.cuh), hence the
+// same bits; what changes is the schedule.  The reference runs 2 + 4*L full-size dispatches per frame over AoS
+// buffers with dead rays left in place (renderer/Renderer.mm:504-584).  Here:
+//   * every owned pixel has one path SLOT whose state (the live fields of Ray / LightSamplingRay / Intersection,
+//     Raytracing.h:54-90) lives in SoA float4 arrays in HBM; a slot that finishes a sample accumulates it
+//     (Shaders.metal:239-248) and starts the next frame's sample at once, so the extension queue stays full;
+//   * k_wf_shade = lightSamplingHandler (Shaders.metal:214-231) of the previous bounce, then intersectionHandler
+//     (:105-212) of this one, then accumulate + rayGenerator (:75-103) when the sample ends; it appends the live
+//     extension / light-sampling rays of the next wave to two queues with warp ballots + one atomic per block;
+//   * k_wf_trace is persistent (one resident grid): warps pull queue entries from a global counter and refill
+//     idle lanes while the others keep traversing (device_trace.cuh: trace_persistent).  Light-sampling rays are
+//     first tested against their target triangle (in k_wf_shade) and then only need "does anything beat
+//     (tTarget, target)?" — the exact predicate of Shaders.metal:225 — so they stop at the first occluder.
+#include <cstdlib>
+#include "kernels.h"
+#include "device_trace.cuh"
+
+namespace mrt {
+
+__device__ __forceinline__ bool wf_owns_row(const Grid2D& g, uint32_t y) { return y % g.rowStride == g.rowFirst; }
+
+// ---- IO policy over a strided AoS ray buffer (the MPS drop-in, Renderer.mm:519-523 / 545-553) -------------------
+struct StridedIO {
+    const char* rays; uint32_t stride; mrt_intersection* out; Grid2D g; bool useGrid, vec;
+    uint32_t live;
+    __device__ __forceinline__ bool load(uint32_t i, TraceJob& job) {
+        if (useGrid && !wf_owns_row(g, i / g.W)) return false;
+        const char* p = rays + (size_t)i * stride;
+        float4 a, b;
+        if (vec) { a = *reinterpret_cast<const float4*>(p); b = *reinterpret_cast<const float4*>(p + 16); }
+        else {
+            const float* f = reinterpret_cast<const float*>(p);
+            a = make_float4(f[0], f[1], f[2], f[3]); b = make_float4(f[4], f[5], f[6], f[7]);
+        }
+        if (!(b.w >= 0.0f)) {                              // skipped ray: reports a miss
+            *reinterpret_cast<float4*>(out + i) = make_float4(-1.0f, __uint_as_float(MRT_NO_HIT), 0.0f, 0.0f);
+            return false;
+        }
+        ++live;
+        job.o = mk3(a.x, a.y, a.z); job.d = mk3(b.x, b.y, b.z); job.tmin = a.w; job.tmax = b.w;
+        job.target = MRT_NO_HIT; job.tag = i;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, uint32_t, const HitRec& h) {
+        *reinterpret_cast<float4*>(out + i) = make_float4(h.t, __uint_as_float(h.tri), h.u, h.v);
+    }
+};
+
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) k_intersect_persistent(DeviceScene S, const char* __restrict__ rays, uint32_t stride,
+                                                                    uint32_t count, mrt_intersection* __restrict__ out, Grid2D g,
+                                                                    bool useGrid, bool vec, unsigned long long* liveCounter,
+                                                                    unsigned int* head, uint32_t refillBelow) {
+    StridedIO io; io.rays = rays; io.stride = stride; io.out = out; io.g = g; io.useGrid = useGrid; io.vec = vec; io.live = 0;
+    trace_persistent(S.nodes, S.tris, count, head, refillBelow, io);
+    if (liveCounter) {
+        uint32_t n = __reduce_add_sync(0xffffffffu, io.live);
+        if ((threadIdx.x & 31) == 0 && n) atomicAdd(liveCounter, (unsigned long long)n);
+    }
+}
+
+// ---- IO policy over the wavefront queues ------------------------------------------------------------------------
+struct WfIO {
+    const float4 *P0, *P1, *S0, *S1;
+    float4* H; uint32_t* visible;
+    const uint32_t *qe, *qs;
+    uint32_t nExt;
+    __device__ __forceinline__ bool load(uint32_t i, TraceJob& job) {
+        if (i < nExt) {                                    // extension ray: nearest hit, [0, inf)  (Renderer.mm:519-523)
+            uint32_t slot = qe[i];
+            float4 a = P0[slot], b = P1[slot];
+            job.o = mk3(a.x, a.y, a.z); job.d = mk3(b.x, b.y, b.z); job.tmin = 0.0f; job.tmax = INFINITY;
+            job.target = MRT_NO_HIT; job.tag = slot;
+        } else {                                           // light-sampling ray, bounded by its target (Renderer.mm:545-553)
+            uint32_t slot = qs[i - nExt];
+            float4 a = P0[slot], b = S0[slot], c = S1[slot];
+            job.o = mk3(a.x, a.y, a.z); job.d = mk3(b.x, b.y, b.z); job.tmin = 0.0f; job.tmax = b.w;
+            job.target = __float_as_uint(c.w); job.tag = slot;
+        }
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t slot, uint32_t target, const HitRec& h) {
+        if (target == MRT_NO_HIT) H[slot] = make_float4(h.t, __uint_as_float(h.tri), h.u, h.v);
+        else visible[slot] = (h.tri == target) ? 1u : 0u;
+    }
+};
+
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers b, uint32_t parity, uint32_t refillBelow,
+                                                        unsigned long long* counters) {
+    const uint32_t nExt = b.counts[2 * parity], nShadow = b.counts[2 * parity + 1];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        // the other queue pair was consumed by the previous wave's trace; clear it for the shade that follows us
+        b.counts[2 * (parity ^ 1u)] = 0; b.counts[2 * (parity ^ 1u) + 1] = 0; b.heads[parity ^ 1u] = 0;
+        if (counters && nExt) atomicAdd(counters, (unsigned long long)nExt);        // live extension rays traversed
+    }
+    WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
+    io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
+    trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, io);
+}
+
+// ---- k_wf_shade: resolve -> intersectionHandler -> accumulate/regenerate, queue compaction ----------------------
+// slot -> pixel: 32 consecutive slots are one 8x4 pixel tile (primary rays of a warp stay coherent).
+template <bool COUNT>
+__global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, uint32_t outParity, uint32_t first) {
+    __shared__ uint32_t sE[8], sS[8], sN[8], sBase[2];
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t tilesX = (P.g.W + 7u) >> 3;
+    const uint32_t tile = slot >> 5;
+    const uint32_t x = (tile % tilesX) * 8u + (lane & 7u);
+    const uint32_t row = (tile / tilesX) * 4u + (lane >> 3);
+    const uint32_t y = P.g.rowFirst + row * P.g.rowStride;
+    const bool valid = slot < b.slots && x < P.g.W && row < P.ownedRows;
+    const size_t tileStride = MRT_NOISE_DIMENSIONS * MRT_NOISE_DIMENSIONS;
+    bool pushE = false, pushS = false;
+    uint32_t liveShadow = 0;
+
+    if (valid) {
+        const uint32_t cw = first ? 0u : b.cursor[slot];
+        uint32_t k = cw & 0x7fffffffu;
+        if (k < P.nFrames) {
+            PathState st;
+            bool gen = first != 0;
+            uint32_t pending = 0;
+            if (!first) {
+                float4 p0 = b.P0[slot], p1 = b.P1[slot], p2 = b.P2[slot], p3 = b.P3[slot];
+                st.origin = mk3(p0.x, p0.y, p0.z); st.pdf = p0.w;
+                st.direction = mk3(p1.x, p1.y, p1.z); st.prevDiffuse = p1.w;
+                st.throughput = mk3(p2.x, p2.y, p2.z); st.bounce = p2.w;
+                st.radiance = mk3(p3.x, p3.y, p3.z); st.ior = p3.w;
+                const uint4 e = __ldg(P.frames + k);
+                if (cw >> 31) {                                                        // Shaders.metal:225-229
+                    if (b.visible[slot]) { float4 s1 = b.S1[slot]; st.radiance = st.radiance + mk3(s1.x, s1.y, s1.z); }
+                }
+                const float4 h = b.H[slot];
+                bool finished;
+                if (h.x < MRT_DISTANCE_EPSILON) {                                      // Shaders.metal:122-126
+                    finished = true;
+                } else {
+                    HitRec hit; hit.t = h.x; hit.tri = __float_as_uint(h.y); hit.u = h.z; hit.v = h.w;
+                    const uint32_t s = (e.x + uint32_t(st.bounce)) % 3u;               // Renderer.mm:538
+                    const uint32_t t = s == 0 ? e.y : (s == 1 ? e.z : e.w);
+                    ShadowRay sh; bool nee;
+                    const bool live = intersection_handler(P.S, hit, st, sh, nee, P.noisePool + t * tileStride, e.x,
+                                                           P.maxPathLength, x, y);
+                    if (live) {
+                        liveShadow = 1;
+                        // the light-sampling ray can only count if it reaches its target at t >= DISTANCE_EPSILON
+                        HitRec tg; tg.t = INFINITY; tg.tri = MRT_NO_HIT; tg.u = tg.v = 0.0f;
+                        triangle_test(P.S.tris, __ldg(b.triSlot + sh.targetIndex), st.origin, sh.direction, 0.0f, INFINITY, tg);
+                        if (tg.tri == sh.targetIndex && tg.t >= MRT_DISTANCE_EPSILON) {
+                            pushS = true; pending = 1;
+                            b.S0[slot] = make_float4(sh.direction.x, sh.direction.y, sh.direction.z, tg.t);
+                            b.S1[slot] = make_float4(sh.throughput.x, sh.throughput.y, sh.throughput.z, __uint_as_float(sh.targetIndex));
+                        }
+                    }
+                    finished = uint32_t(st.bounce) >= P.maxPathLength;
+                }
+                if (finished) {                                                        // Shaders.metal:239-248
+                    const uint32_t pix = y * P.g.W + x;
+                    const float4 c = P.image[pix];
+                    const f3 color = accumulate_image(st.radiance, mk3(c.x, c.y, c.z), e.x, P.accumMode);
+                    P.image[pix] = make_float4(color.x, color.y, color.z, 1.0f);
+                    ++k; gen = true; pending = 0; pushS = false;
+                }
+            }
+            if (gen) {
+                if (k < P.nFrames) {
+                    const uint4 e = __ldg(P.frames + k);
+                    const uint32_t s = e.x % 3u;
+                    const uint32_t t = s == 0 ? e.y : (s == 1 ? e.z : e.w);
+                    ray_generator(st, P.noisePool + t * tileStride, x, y, P.g.W, P.g.H);   // Renderer.mm:508-512
+                    pushE = true;
+                }
+            } else {
+                pushE = true;
+            }
+            if (pushE) {
+                b.P0[slot] = make_float4(st.origin.x, st.origin.y, st.origin.z, st.pdf);
+                b.P1[slot] = make_float4(st.direction.x, st.direction.y, st.direction.z, st.prevDiffuse);
+                b.P2[slot] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.bounce);
+                b.P3[slot] = make_float4(st.radiance.x, st.radiance.y, st.radiance.z, st.ior);
+            }
+            b.cursor[slot] = k | (pending << 31);
+        }
+    }
+
+    // ---- append to the next wave's queues: warp ballots, one atomic per block and queue ----
+    const unsigned mE = __ballot_sync(0xffffffffu, pushE), mS = __ballot_sync(0xffffffffu, pushS);
+    const uint32_t nLive = COUNT ? __reduce_add_sync(0xffffffffu, liveShadow) : 0u;
+    if (lane == 0) { sE[warp] = __popc(mE); sS[warp] = __popc(mS); sN[warp] = nLive; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t aE = 0, aS = 0, aN = 0;
+        for (int w = 0; w < 8; ++w) { uint32_t e = sE[w], s = sS[w]; sE[w] = aE; sS[w] = aS; aE += e; aS += s; aN += sN[w]; }
+        sBase[0] = aE ? atomicAdd(b.counts + 2 * outParity, aE) : 0u;
+        sBase[1] = aS ? atomicAdd(b.counts + 2 * outParity + 1, aS) : 0u;
+        if (COUNT && aN) atomicAdd(P.counters + 1, (unsigned long long)aN);           // live light-sampling rays
+    }
+    __syncthreads();
+    const unsigned lt = (1u << lane) - 1u;
+    if (pushE) b.queueExt[outParity][sBase[0] + sE[warp] + __popc(mE & lt)] = slot;
+    if (pushS) b.queueShadow[outParity][sBase[1] + sS[warp] + __popc(mS & lt)] = slot;
+}
+
+// ---- launchers ---------------------------------------------------------------------------------------------------
+static int env_int(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
+static int device_sms() {
+    int dev = 0, n = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n > 0 ? n : 148;
+}
+struct TraceTuning { int minb, refill; };
+static TraceTuning trace_tuning() {
+    static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", 8), env_int("MRT_TRACE_REFILL", 24) };
+    return t;
+}
+
+void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const void* rays, uint32_t strideBytes, uint32_t count,
+                                 mrt_intersection* out, Grid2D g, bool useGrid, unsigned long long* liveCounter,
+                                 unsigned int* head) {
+    if (count == 0) return;
+    const bool vec = (strideBytes % 16u == 0) && ((uintptr_t)rays % 16u == 0);
+    const TraceTuning t = trace_tuning();
+    const char* r = static_cast<const char*>(rays);
+    const uint32_t warpsNeeded = (count + 31u) / 32u;
+    const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
+    auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); uint32_t need = (warpsNeeded + 3u) / 4u; return need < cap ? need : cap; };
+    if (t.minb >= 16)      k_intersect_persistent<16><<<blocks(16), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
+    else if (t.minb >= 12) k_intersect_persistent<12><<<blocks(12), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
+    else if (t.minb >= 10) k_intersect_persistent<10><<<blocks(10), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
+    else if (t.minb >= 8)  k_intersect_persistent<8><<<blocks(8), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
+    else                   k_intersect_persistent<6><<<blocks(6), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
+}
+
+void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave) {
+    const TraceTuning t = trace_tuning();
+    const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
+    const uint32_t parity = wave & 1u;
+    const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
+    auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
+    if (t.minb >= 16)      k_wf_trace<16><<<blocks(16), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
+    else if (t.minb >= 12) k_wf_trace<12><<<blocks(12), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
+    else if (t.minb >= 10) k_wf_trace<10><<<blocks(10), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
+    else if (t.minb >= 8)  k_wf_trace<8><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
+    else                   k_wf_trace<6><<<blocks(6), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
+}
+
+void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays) {
+    if (b.slots == 0) return;
+    const uint32_t blocks = (b.slots + 255u) / 256u;
+    const uint32_t outParity = first ? 0u : ((wave + 1u) & 1u);               // shade(w) fills the queues trace(w+1) consumes
+    if (countRays) k_wf_shade<true><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u);
+    else           k_wf_shade<false><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u);
+}
+
+int wf_kernel_info(int* traceRegs, int* traceBlocksPerSM, int* shadeRegs) {
+    cudaFuncAttributes a;
+    cudaError_t e = cudaFuncGetAttributes(&a, k_wf_trace<8>);
+    if (e != cudaSuccess) return (int)e;
+    *traceRegs = a.numRegs;
+    e = cudaFuncGetAttributes(&a, k_wf_shade<true>);
+    if (e != cudaSuccess) return (int)e;
+    *shadeRegs = a.numRegs;
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(traceBlocksPerSM, k_wf_trace<8>, 128, 0);
+}
+
+}  // namespace mrt

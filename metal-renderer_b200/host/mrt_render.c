@@ -7,7 +7,7 @@
  * second, Renderer.mm:631-637) plus live ray segments per second.
  *
  * usage: mrt_render [--scene NAME|file.obj] [--size WxH] [--frames N] [--depth L] [--seed S] [--device D]
- *                   [--pipeline fused|staged] [--out image.pfm]
+ *                   [--pipeline auto|wavefront|fused|staged] [--out image.pfm]
  */
 #define _POSIX_C_SOURCE 200809L
 #include <stdio.h>
@@ -33,7 +33,7 @@ static int write_pfm(const char* path, const float* rgba, unsigned w, unsigned h
 int main(int argc, char** argv) {
     const char* scene_name = "cornell";
     const char* out = NULL;
-    unsigned w = 256, h = 256, frames = 16, depth = MRT_MAX_PATH_LENGTH, device = 0, staged = 0;
+    unsigned w = 256, h = 256, frames = 16, depth = MRT_MAX_PATH_LENGTH, device = 0, pipeline = MRT_PIPELINE_AUTO;
     unsigned long long seed = 1;
     for (int i = 1; i < argc; ++i) {
         const char* a = argv[i];
@@ -44,7 +44,11 @@ int main(int argc, char** argv) {
         else if (!strcmp(a, "--depth")) { depth = (unsigned)atoi(v); ++i; }
         else if (!strcmp(a, "--seed")) { seed = strtoull(v, NULL, 10); ++i; }
         else if (!strcmp(a, "--device")) { device = (unsigned)atoi(v); ++i; }
-        else if (!strcmp(a, "--pipeline")) { staged = !strcmp(v, "staged"); ++i; }
+        else if (!strcmp(a, "--pipeline")) {
+            pipeline = !strcmp(v, "staged") ? MRT_PIPELINE_STAGED : !strcmp(v, "fused") ? MRT_PIPELINE_MEGAKERNEL
+                     : !strcmp(v, "wavefront") ? MRT_PIPELINE_WAVEFRONT : MRT_PIPELINE_AUTO;
+            ++i;
+        }
         else if (!strcmp(a, "--out")) { out = v; ++i; }
         else { fprintf(stderr, "unknown argument %s\n", a); return 2; }
     }
@@ -60,7 +64,7 @@ int main(int argc, char** argv) {
     mrt_config_default(&cfg);
     cfg.device = (int)device;
     cfg.max_path_length = depth;
-    cfg.pipeline = staged ? MRT_PIPELINE_WAVEFRONT : MRT_PIPELINE_AUTO;
+    cfg.pipeline = pipeline;
     mrt_ctx* ctx = NULL;
     CHECK(mrt_create(&cfg, &ctx));
     CHECK(mrt_set_scene_from(ctx, scene));

@@ -31,7 +31,7 @@ NOISE_DIMENSIONS = 64
 NOISE_TILE_FLOATS = 4 * NOISE_DIMENSIONS * NOISE_DIMENSIONS
 NOT_A_LIGHT = 0xFFFFFFFF
 MATERIAL_DIFFUSE, MATERIAL_MIRROR, MATERIAL_SMOOTH_PLASTIC, MATERIAL_SMOOTH_DIELECTRIC = range(4)
-PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT = range(3)
+PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_STAGED = range(4)
 ACCUM_MEAN, ACCUM_SUM, ACCUM_REPLACE = range(3)
 BUF_RAYS, BUF_LIGHT_RAYS, BUF_INTERSECTIONS, BUF_IMAGE = range(4)
 BUFFER_DTYPES = {BUF_RAYS: RAY, BUF_LIGHT_RAYS: LIGHT_RAY, BUF_INTERSECTIONS: INTERSECTION}

@@ -1,5 +1,5 @@
 """Full-size GPU checks at BASELINE.json's sizes, through size-independent properties (the oracle would take
-minutes here): fused megakernel == the reference-shaped 34-dispatch sequence bit-for-bit, row shards compose,
+minutes here): wavefront == megakernel == the reference-shaped 34-dispatch sequence bit-for-bit, row shards compose,
 traversal == brute-force definition on sampled rays, ray accounting."""
 import numpy as np
 import pytest
@@ -24,13 +24,14 @@ def gpu_renderer(scene, w, h, L=8, **kw):
 def test_1080p_fused_equals_staged(name, seed):
     scene = m.Scene.procedural(name, seed)
     tiles = m.noise_tiles(seed, 0, 3)
-    a = gpu_renderer(scene, 1920, 1080)
-    b = gpu_renderer(scene, 1920, 1080, pipeline=m.PIPELINE_WAVEFRONT)
-    a.draw(3, tiles); b.draw(3, tiles)
-    ia, ib = a.save_current_image(), b.save_current_image()
-    assert bits_equal(ia, ib)
-    sa, sb = a.stats(), b.stats()
-    assert (sa["primary_rays"], sa["shadow_rays"]) == (sb["primary_rays"], sb["shadow_rays"])
+    a = gpu_renderer(scene, 1920, 1080, pipeline=m.PIPELINE_WAVEFRONT)
+    b = gpu_renderer(scene, 1920, 1080, pipeline=m.PIPELINE_STAGED)
+    c = gpu_renderer(scene, 1920, 1080, pipeline=m.PIPELINE_MEGAKERNEL)
+    a.draw(3, tiles); b.draw(3, tiles); c.draw(3, tiles)
+    ia, ib, ic = a.save_current_image(), b.save_current_image(), c.save_current_image()
+    assert bits_equal(ia, ib) and bits_equal(ic, ib)
+    sa, sb, sc = a.stats(), b.stats(), c.stats()
+    assert (sa["primary_rays"], sa["shadow_rays"]) == (sb["primary_rays"], sb["shadow_rays"]) == (sc["primary_rays"], sc["shadow_rays"])
     n = 1920 * 1080 * 3
     assert n <= sa["primary_rays"] <= 8 * n and 0 < sa["shadow_rays"] <= 7 * n
     finite = np.isfinite(ia[..., :3])

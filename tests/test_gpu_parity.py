@@ -74,15 +74,19 @@ def render_both(scene, w, h, frames, L, seed, pipeline=m.PIPELINE_AUTO, **kw):
     return r, o
 
 
-def test_config1_cornell_256_16spp_depth4_bit_exact():
+PIPES = [pytest.param(m.PIPELINE_WAVEFRONT, id="wavefront"), pytest.param(m.PIPELINE_MEGAKERNEL, id="megakernel")]
+
+
+@pytest.mark.parametrize("pipeline", PIPES)
+def test_config1_cornell_256_16spp_depth4_bit_exact(pipeline):
     """BASELINE.json configs[0]: procedural Cornell 256x256, 16 spp, max depth 4."""
     scene = m.Scene.procedural("cornell", 0)
-    r, o = render_both(scene, 256, 256, 16, 4, seed=1)
+    r, o = render_both(scene, 256, 256, 16, 4, seed=1, pipeline=pipeline)
     gi, oi = r.save_current_image(), o.save_current_image()
     assert_bits(gi, oi, "image")
     st, oc = r.stats(), o.counts()
     assert (st["primary_rays"], st["shadow_rays"]) == (oc["primary_rays"], oc["shadow_rays"])
-    assert st["kernel_launches"] == 1
+    assert st["kernel_launches"] == (1 if pipeline == m.PIPELINE_MEGAKERNEL else 1 + 2 * 16 * 4)
     # primary-hit triangle IDs: bit-equal on 100% of pixels
     r2, o2 = setup_pair(scene, 256, 256)
     r2.raygen(0); o2.raygen(0); r2.intersect(); o2.intersect()
@@ -91,62 +95,70 @@ def test_config1_cornell_256_16spp_depth4_bit_exact():
 
 @pytest.mark.parametrize("name,w,h,frames,L", [("cornell-water", 160, 90, 6, 8), ("spheres-64k", 128, 72, 4, 8),
                                                 ("many-lights", 96, 54, 4, 8), ("white-box", 64, 64, 5, 3)])
-def test_fused_render_bit_exact(name, w, h, frames, L):
+@pytest.mark.parametrize("pipeline", PIPES)
+def test_production_render_bit_exact(name, w, h, frames, L, pipeline):
     scene = m.Scene.procedural(name, 5)
-    r, o = render_both(scene, w, h, frames, L, seed=7)
+    r, o = render_both(scene, w, h, frames, L, seed=7, pipeline=pipeline)
     assert_bits(r.save_current_image(), o.save_current_image(), name)
     st, oc = r.stats(), o.counts()
     assert (st["primary_rays"], st["shadow_rays"]) == (oc["primary_rays"], oc["shadow_rays"])
 
 
-def test_wavefront_pipeline_and_continuation_bit_exact():
+def test_staged_pipeline_and_continuation_bit_exact():
     scene = m.Scene.procedural("cornell-water", 0)
     w, h, L = 120, 68, 6
     tiles = m.noise_tiles(3, 0, 7)
-    a, o = setup_pair(scene, w, h, max_path_length=L)                                   # fused, in two batches
-    b, _ = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(pipeline=m.PIPELINE_WAVEFRONT))
-    a.draw(3, tiles[:3]); a.draw(4, tiles[3:])                                           # slots carry over between calls
+    a, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(pipeline=m.PIPELINE_WAVEFRONT))
+    c, _ = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(pipeline=m.PIPELINE_MEGAKERNEL))
+    b, _ = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(pipeline=m.PIPELINE_STAGED))
+    a.draw(3, tiles[:3]); a.draw(4, tiles[3:])                                           # noise slots carry over between calls
+    c.draw(3, tiles[:3]); c.draw(4, tiles[3:])
     b.draw(7, tiles)
     o.draw(7, tiles)
     want = o.save_current_image()
-    assert_bits(a.save_current_image(), want, "fused 3+4")
-    assert_bits(b.save_current_image(), want, "wavefront")
+    assert_bits(a.save_current_image(), want, "wavefront 3+4")
+    assert_bits(c.save_current_image(), want, "megakernel 3+4")
+    assert_bits(b.save_current_image(), want, "staged")
     assert b.stats()["kernel_launches"] == 7 * (2 + 4 * L)
+    sa, sb, sc = a.stats(), b.stats(), c.stats()
+    assert (sa["primary_rays"], sa["shadow_rays"]) == (sb["primary_rays"], sb["shadow_rays"]) == (sc["primary_rays"], sc["shadow_rays"])
 
 
-def test_noise_zero_produces_identical_nans():
+@pytest.mark.parametrize("pipeline", PIPES)
+def test_noise_zero_produces_identical_nans(pipeline):
     # noise.w == 0 makes bsdf/pdf = 0/0 (Shaders.metal:209): the NaNs must appear in the same pixels
     scene = m.Scene.procedural("cornell", 0)
     tiles = m.noise_tiles(2, 0, 3).copy()
     tiles[:, 3::4][:, ::5] = 0.0
     tiles[:, 2::4][:, ::7] = 0.0
-    r, o = setup_pair(scene, 64, 64, max_path_length=4)
+    r, o = setup_pair(scene, 64, 64, max_path_length=4, renderer_kwargs=dict(pipeline=pipeline))
     r.draw(3, tiles); o.draw(3, tiles)
     gi, oi = r.save_current_image(), o.save_current_image()
     assert_bits(gi, oi, "image with NaNs")
 
 
-def test_accumulate_modes_and_row_shards():
+@pytest.mark.parametrize("pipeline", PIPES)
+def test_accumulate_modes_and_row_shards(pipeline):
     scene = m.Scene.procedural("cornell", 0)
     w, h, L = 64, 48, 4
     tiles = m.noise_tiles(8, 0, 4)
     for mode in (m.ACCUM_SUM, m.ACCUM_REPLACE):
-        r, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(accumulate_mode=mode))
+        r, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(accumulate_mode=mode, pipeline=pipeline))
         o.set_accumulate_mode(mode)
         r.draw(4, tiles); o.draw(4, tiles)
         assert_bits(r.save_current_image(), o.save_current_image(), f"mode {mode}")
     # row sharding: 3 shards compose to the unsharded image bit-for-bit; strided frames match the oracle
-    full, o = setup_pair(scene, w, h, max_path_length=L)
+    full, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(pipeline=pipeline))
     full.draw(4, tiles)
     ref = full.save_current_image()
     acc = np.zeros_like(ref)
     for g in range(3):
-        r, _ = setup_pair(scene, w, h, max_path_length=L)
+        r, _ = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(pipeline=pipeline))
         r.set_row_shard(g, 3)
         r.draw(4, tiles)
         acc[g::3] = r.save_current_image()[g::3]
     assert_bits(acc, ref, "row shards")
-    r, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(accumulate_mode=m.ACCUM_SUM))
+    r, o = setup_pair(scene, w, h, max_path_length=L, renderer_kwargs=dict(accumulate_mode=m.ACCUM_SUM, pipeline=pipeline))
     o.set_accumulate_mode(m.ACCUM_SUM)
     r.draw(2, tiles, first_frame=1, frame_stride=2); o.draw(2, tiles, first_frame=1, frame_stride=2)   # frames 1, 3
     assert_bits(r.save_current_image(), o.save_current_image(), "strided frames")
