@@ -124,7 +124,7 @@ struct TraceJob {
 
 template <class IO>
 __device__ __forceinline__ void trace_persistent(const float4* __restrict__ nodes, const float4* __restrict__ tris,
-                                                 uint32_t total, unsigned int* head, uint32_t refillBelow, IO& io) {
+                                                 uint32_t total, unsigned int* head, uint32_t refillBelow, uint32_t leafMin, IO& io) {
     const uint32_t lane = threadIdx.x & 31u;
     const float tiny = 1e-30f;
     bool alive = false, exhausted = (total == 0);
@@ -166,10 +166,19 @@ __device__ __forceinline__ void trace_persistent(const float4* __restrict__ node
         }
         if (am == 0) break;                               // queue empty and every lane idle
 
-        // ---- traverse: each round takes a lane to its next leaf and through it ----
+        // ---- traverse.  Every round the warp votes: lanes standing on an inner node want a NODE step, lanes
+        // standing on a leaf (or on the end marker) want a LEAF step.  Node steps outnumber leaf steps ~10:1,
+        // so the warp keeps taking node steps — with every lane that wants one — until at least `leafMin` lanes
+        // are parked on leaves (or nobody wants a node); only then is the leaf code run.  A per-lane
+        // "descend until the next leaf" loop instead makes the warp wait for its slowest descender each round
+        // (ncu: 8.3 of 32 lanes active in the node loop). ----
         for (;;) {
-            if (alive) {
-                while (cur >= 0) {
+            const bool wantNode = alive && cur >= 0;
+            const unsigned mN = __ballot_sync(0xffffffffu, wantNode);
+            const unsigned mL = __ballot_sync(0xffffffffu, alive && cur < 0);
+            if ((mN | mL) == 0) break;
+            if (mN != 0 && __popc(mL) < (int)leafMin) {
+                if (wantNode) {
                     const float4* np = nodes + 4 * (size_t)cur;
                     float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
                     float c0x0 = __fmaf_rn(n0.x, idx, -ox), c0x1 = __fmaf_rn(n0.y, idx, -ox);
@@ -182,7 +191,7 @@ __device__ __forceinline__ void trace_persistent(const float4* __restrict__ node
                     float tf0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), best.t));
                     float tn1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
                     float tf1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), best.t));
-                    bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+                    bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;       // non-strict: equal-t ties must still be tested
                     int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
                     if (h0 && h1) {
                         if (tn1 < tn0) { int t = c0; c0 = c1; c1 = t; }
@@ -194,6 +203,9 @@ __device__ __forceinline__ void trace_persistent(const float4* __restrict__ node
                         cur = stack[--sp];
                     }
                 }
+                continue;
+            }
+            if (alive && cur < 0) {
                 if (cur != MRT_TRACE_DONE) {
                     uint32_t code = ~uint32_t(cur);
                     uint32_t first = code >> 3, count = code & 7u;

@@ -52,9 +52,9 @@ template <int MINB>
 __global__ void __launch_bounds__(128, MINB) k_intersect_persistent(DeviceScene S, const char* __restrict__ rays, uint32_t stride,
                                                                     uint32_t count, mrt_intersection* __restrict__ out, Grid2D g,
                                                                     bool useGrid, bool vec, unsigned long long* liveCounter,
-                                                                    unsigned int* head, uint32_t refillBelow) {
+                                                                    unsigned int* head, uint32_t refillBelow, uint32_t leafMin) {
     StridedIO io; io.rays = rays; io.stride = stride; io.out = out; io.g = g; io.useGrid = useGrid; io.vec = vec; io.live = 0;
-    trace_persistent(S.nodes, S.tris, count, head, refillBelow, io);
+    trace_persistent(S.nodes, S.tris, count, head, refillBelow, leafMin, io);
     if (liveCounter) {
         uint32_t n = __reduce_add_sync(0xffffffffu, io.live);
         if ((threadIdx.x & 31) == 0 && n) atomicAdd(liveCounter, (unsigned long long)n);
@@ -89,7 +89,7 @@ struct WfIO {
 
 template <int MINB>
 __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers b, uint32_t parity, uint32_t refillBelow,
-                                                        unsigned long long* counters) {
+                                                        uint32_t leafMin, unsigned long long* counters) {
     const uint32_t nExt = b.counts[2 * parity], nShadow = b.counts[2 * parity + 1];
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // the other queue pair was consumed by the previous wave's trace; clear it for the shade that follows us
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     }
     WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
-    trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, io);
+    trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
 }
 
 // ---- k_wf_shade: resolve -> intersectionHandler -> accumulate/regenerate, queue compaction ----------------------
@@ -214,9 +214,9 @@ static int device_sms() {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     return n > 0 ? n : 148;
 }
-struct TraceTuning { int minb, refill; };
+struct TraceTuning { int minb, refill, leafMin; };
 static TraceTuning trace_tuning() {
-    static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", 8), env_int("MRT_TRACE_REFILL", 24) };
+    static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", 10), env_int("MRT_TRACE_REFILL", 24), env_int("MRT_TRACE_LEAFMIN", 8) };
     return t;
 }
 
@@ -229,25 +229,27 @@ void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const voi
     const char* r = static_cast<const char*>(rays);
     const uint32_t warpsNeeded = (count + 31u) / 32u;
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
+    const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin));
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); uint32_t need = (warpsNeeded + 3u) / 4u; return need < cap ? need : cap; };
-    if (t.minb >= 16)      k_intersect_persistent<16><<<blocks(16), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
-    else if (t.minb >= 12) k_intersect_persistent<12><<<blocks(12), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
-    else if (t.minb >= 10) k_intersect_persistent<10><<<blocks(10), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
-    else if (t.minb >= 8)  k_intersect_persistent<8><<<blocks(8), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
-    else                   k_intersect_persistent<6><<<blocks(6), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill);
+    if (t.minb >= 16)      k_intersect_persistent<16><<<blocks(16), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
+    else if (t.minb >= 12) k_intersect_persistent<12><<<blocks(12), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
+    else if (t.minb >= 10) k_intersect_persistent<10><<<blocks(10), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
+    else if (t.minb >= 8)  k_intersect_persistent<8><<<blocks(8), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
+    else                   k_intersect_persistent<6><<<blocks(6), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
 }
 
 void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave) {
     const TraceTuning t = trace_tuning();
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
+    const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin));
     const uint32_t parity = wave & 1u;
     const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
-    if (t.minb >= 16)      k_wf_trace<16><<<blocks(16), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
-    else if (t.minb >= 12) k_wf_trace<12><<<blocks(12), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
-    else if (t.minb >= 10) k_wf_trace<10><<<blocks(10), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
-    else if (t.minb >= 8)  k_wf_trace<8><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
-    else                   k_wf_trace<6><<<blocks(6), 128, 0, s>>>(p.S, b, parity, refill, p.counters);
+    if (t.minb >= 16)      k_wf_trace<16><<<blocks(16), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
+    else if (t.minb >= 12) k_wf_trace<12><<<blocks(12), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
+    else if (t.minb >= 10) k_wf_trace<10><<<blocks(10), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
+    else if (t.minb >= 8)  k_wf_trace<8><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
+    else                   k_wf_trace<6><<<blocks(6), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
 }
 
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays) {
