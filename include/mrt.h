@@ -90,8 +90,10 @@ typedef struct mrt_stats {
     uint32_t bvh_depth;
     float    bvh_sah_cost;
     float    bvh_build_ms;      /* host wall time of the last SAH build */
-    float    last_kernel_ms;    /* device time of the fused kernel alone inside the last mrt_render_frames */
-    uint32_t reserved[4];
+    float    last_kernel_ms;    /* device time of the kernels alone inside the last mrt_render_frames */
+    uint32_t bvh8_nodes;        /* 8-wide quantised tree the production trace kernel traverses (80-byte nodes) */
+    uint32_t bvh8_depth;
+    uint32_t reserved[2];
 } mrt_stats;
 
 /* Read-only view of a host scene container (arrays in the ABI layouts of mrt_abi.h). */
@@ -206,6 +208,16 @@ int  mrt_scene_create_procedural(const char* name, uint64_t seed, mrt_scene** ou
 int  mrt_scene_load_obj(const char* obj_path, mrt_scene** out);
 int  mrt_scene_get(const mrt_scene* scene, mrt_scene_view* view);
 void mrt_scene_destroy(mrt_scene* scene);
+/* Host-only self-test of the acceleration structure (no GPU needed): builds the 8-wide BVH the kernels traverse,
+ * sends n_rays seeded random rays (some axis-parallel, some starting on box planes) through a host copy of the
+ * traversal state machine — same node decode as the CUDA kernel — and compares every (distance, triangle) with brute
+ * force over all triangles.  Stands where MPSTriangleAccelerationStructure would simply be trusted (Renderer.mm:456-462). */
+typedef struct mrt_bvh_report {
+    uint32_t nodes, depth, triangles, mismatches;
+    float    sah_cost, build_ms;
+    float    nodes_per_ray, triangles_per_ray;
+} mrt_bvh_report;
+int  mrt_bvh_selftest(const mrt_scene* scene, uint32_t n_rays, uint64_t seed, mrt_bvh_report* out);
 /* Noise tile for (seed, frame): 64*64*4 floats, (mt19937_64(seed ^ frame)() >> 40) * 2^-24.
  * Stands in for the clock-seeded fills of Renderer.mm:109-126, 486-495. */
 void mrt_noise_fill(uint64_t seed, uint32_t frame, float* tile);

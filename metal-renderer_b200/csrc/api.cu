@@ -12,6 +12,8 @@
 #include <string>
 #include <vector>
 #include "bvh.h"
+#include "bvh8.h"
+#include <random>
 #include "kernels.h"
 #include "mrt.h"
 #include "scene.h"
@@ -55,6 +57,7 @@ struct mrt_ctx {
     unsigned long long* dCounters = nullptr;     // primary, shadow, nodes, tris
     unsigned int* dHead = nullptr;               // work counter of the persistent intersector (staged entry points)
     void* dTriSlot = nullptr;                    // original triangle index -> leaf-order record
+    void* dNodes8 = nullptr; void* dTris8 = nullptr;   // 8-wide tree (bvh8.h)
     WfBuffers wf{};                              // wavefront path state + queues (sized by mrt_resize)
     void* wfArena = nullptr;
     mrt_stats stats{};
@@ -65,17 +68,18 @@ struct mrt_ctx {
 
 static void free_scene(mrt_ctx* c) {
     cudaFree(c->dNodes); cudaFree(c->dTris); cudaFree(c->dShade); cudaFree(c->dMats); cudaFree(c->dLights); cudaFree(c->dCdf);
-    cudaFree(c->dTriSlot);
+    cudaFree(c->dTriSlot); cudaFree(c->dNodes8); cudaFree(c->dTris8);
+    c->dNodes8 = c->dTris8 = nullptr;
     c->dNodes = c->dTris = c->dShade = c->dMats = c->dLights = c->dCdf = c->dTriSlot = nullptr;
-    c->wf.triSlot = nullptr;
+    c->wf.triSlot = nullptr; c->wf.triRecords = nullptr;
     c->haveScene = false;
 }
 static void free_sized(mrt_ctx* c) {
     cudaFree(c->dRays); cudaFree(c->dLightRays); cudaFree(c->dIsects); cudaFree(c->dImage); cudaFree(c->wfArena);
     c->dRays = nullptr; c->dLightRays = nullptr; c->dIsects = nullptr; c->dImage = nullptr; c->wfArena = nullptr;
-    const uint32_t* triSlot = c->wf.triSlot;
+    const uint32_t* triSlot = c->wf.triSlot; const float4* triRecords = c->wf.triRecords;
     c->wf = WfBuffers{};
-    c->wf.triSlot = triSlot;
+    c->wf.triSlot = triSlot; c->wf.triRecords = triRecords;
 }
 static int ensure_pool(mrt_ctx* c, size_t tiles) {
     if (tiles <= c->poolTiles) return MRT_OK;
@@ -221,10 +225,20 @@ int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count,
     CK(upload(&c->dMats, mats.data(), mats.size() * 4));
     CK(upload(&c->dLights, lts.data(), lts.size() * 4));
     CK(upload(&c->dCdf, cdf.data(), cdf.size() * 4));
+    Bvh8Result bvh8;
+    build_bvh8(vertices, indices, triangle_count, c->cfg.bvh_threads, bvh8);
+    NEED(bvh8.depth + 2 < 32, MRT_E_INVALID, "wide BVH depth %u exceeds traversal stack", bvh8.depth);
+    CK(upload(&c->dNodes8, bvh8.nodes.data(), bvh8.nodes.size() * sizeof(Bvh8Node)));
+    CK(upload(&c->dTris8, bvh8.tris.data(), bvh8.tris.size() * sizeof(BvhTri)));
+    c->S.nodes8 = (const float4*)c->dNodes8; c->S.tris8 = (const float4*)c->dTris8;
+    const bool wide = trace_uses_wide_bvh();
+    const std::vector<BvhTri>& order = wide ? bvh8.tris : bvh.tris;
     std::vector<uint32_t> triSlot(std::max(1u, triangle_count), 0u);
-    for (size_t k = 0; k < bvh.tris.size(); ++k) triSlot[bvh.tris[k].index] = (uint32_t)k;
+    for (size_t k = 0; k < order.size(); ++k) triSlot[order[k].index] = (uint32_t)k;
     CK(upload(&c->dTriSlot, triSlot.data(), triSlot.size() * 4));
     c->wf.triSlot = (const uint32_t*)c->dTriSlot;
+    c->wf.triRecords = (const float4*)(wide ? c->dTris8 : c->dTris);
+    c->stats.bvh8_nodes = (uint32_t)bvh8.nodes.size(); c->stats.bvh8_depth = bvh8.depth;
     c->S.nodes = (const float4*)c->dNodes; c->S.tris = (const float4*)c->dTris; c->S.shadeTris = (const float4*)c->dShade;
     c->S.materials = (const float4*)c->dMats; c->S.lights = (const float4*)c->dLights; c->S.lightCdf = (const float*)c->dCdf;
     c->S.lightCount = light_count; c->S.triangleCount = triangle_count;
@@ -593,6 +607,43 @@ int mrt_scene_get(const mrt_scene* s, mrt_scene_view* v) {
     return MRT_OK;
 }
 void mrt_scene_destroy(mrt_scene* s) { delete s; }
+
+int mrt_bvh_selftest(const mrt_scene* s, uint32_t n_rays, uint64_t seed, mrt_bvh_report* out) {
+    NEED(s && out, MRT_E_INVALID, "NULL argument");
+    const uint32_t ntri = (uint32_t)s->references.size();
+    Bvh8Result bvh;
+    build_bvh8(s->vertices.data(), s->indices.data(), ntri, 0, bvh);
+    float lo[3] = {-1.0f, -1.0f, -1.0f}, hi[3] = {1.0f, 1.0f, 1.0f};
+    if (!s->vertices.empty()) {
+        for (int a = 0; a < 3; ++a) { lo[a] = 1e30f; hi[a] = -1e30f; }
+        for (const mrt_vertex& v : s->vertices) for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], v.v[a]); hi[a] = std::max(hi[a], v.v[a]); }
+    }
+    std::mt19937_64 rng(seed);
+    auto uni = [&]() { return float(rng() >> 40) * (1.0f / 16777216.0f); };
+    std::vector<float> rays(8 * (size_t)n_rays);
+    for (uint32_t i = 0; i < n_rays; ++i) {
+        float* r = &rays[8 * (size_t)i];
+        for (int a = 0; a < 3; ++a) r[a] = lo[a] + (hi[a] - lo[a]) * (uni() * 1.2f - 0.1f);
+        float d[3], len;
+        do { for (int a = 0; a < 3; ++a) d[a] = uni() * 2.0f - 1.0f; len = std::sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]); } while (len < 1e-3f || len > 1.0f);
+        for (int a = 0; a < 3; ++a) d[a] /= len;
+        if (i % 11 == 3) { int a = int(i / 11) % 3; d[a] = 0.0f; }                       // axis-parallel components
+        if (i % 13 == 5) { int a = int(i / 13) % 3; d[0] = d[1] = d[2] = 0.0f; d[a] = (i & 1) ? 1.0f : -1.0f; }
+        if (i % 17 == 7 && !s->vertices.empty()) {                                      // origin exactly on a vertex plane
+            const mrt_vertex& v = s->vertices[rng() % s->vertices.size()]; int a = int(i / 17) % 3; r[a] = v.v[a];
+        }
+        r[3] = (i % 19 == 2) ? 0.25f : 0.0f;
+        r[4] = d[0]; r[5] = d[1]; r[6] = d[2];
+        r[7] = (i % 23 == 4) ? 0.8f : INFINITY;
+    }
+    uint64_t nv = 0, tt = 0;
+    out->mismatches = bvh8_selftest(bvh, rays.data(), n_rays, &nv, &tt);
+    out->nodes = (uint32_t)bvh.nodes.size(); out->depth = bvh.depth; out->triangles = (uint32_t)bvh.tris.size();
+    out->sah_cost = bvh.sah_cost; out->build_ms = (float)bvh.build_ms;
+    out->nodes_per_ray = n_rays ? float(double(nv) / n_rays) : 0.0f;
+    out->triangles_per_ray = n_rays ? float(double(tt) / n_rays) : 0.0f;
+    return MRT_OK;
+}
 void mrt_noise_fill(uint64_t seed, uint32_t frame, float* tile) { noise_fill(seed, frame, tile); }
 
 }  // extern "C"

@@ -8,6 +8,7 @@
 // mathematical near-miss still reaches its triangle: with that, traversal returns exactly
 // min over all triangles of (t, triangle index), independent of the tree (tests check against brute force).
 #include "bvh.h"
+#include "bvh8.h"
 #include <algorithm>
 #include <atomic>
 #include <cfloat>
@@ -126,14 +127,17 @@ struct Builder {
 
 }  // namespace
 
-void build_bvh(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, uint32_t maxLeaf, uint32_t threads,
-               BvhResult& out) {
-    auto t0 = std::chrono::steady_clock::now();
-    out = BvhResult();
-    if (maxLeaf < 1) maxLeaf = 1;
-    if (maxLeaf > 7) maxLeaf = 7;
+// Triangle bounds, conservative padding and the binned-SAH binary tree (sparse implicit layout) shared by the
+// BVH2 emitter below and the 8-wide collapse of build_bvh8.
+struct Front {
+    std::vector<float> tlo, thi;
+    Builder b;
+    float pad = 0.0f;
+};
+static void build_front(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, uint32_t maxLeaf, uint32_t threads, Front& f) {
     if (threads == 0) threads = std::max(1u, std::thread::hardware_concurrency());
-    std::vector<float> tlo(3 * size_t(n)), thi(3 * size_t(n));
+    f.tlo.resize(3 * size_t(n)); f.thi.resize(3 * size_t(n));
+    std::vector<float>& tlo = f.tlo; std::vector<float>& thi = f.thi;
     Box scene; scene.reset();
     for (uint32_t t = 0; t < n; ++t) {
         const float* p0 = vertices[indices[3 * size_t(t)]].v; const float* p1 = vertices[indices[3 * size_t(t) + 1]].v;
@@ -146,22 +150,9 @@ void build_bvh(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, 
     }
     float ext = 0.0f, mag = 0.0f;
     for (int a = 0; a < 3 && n; ++a) { ext = std::max(ext, scene.hi[a] - scene.lo[a]); mag = std::max(mag, std::max(std::fabs(scene.lo[a]), std::fabs(scene.hi[a]))); }
-    out.pad = 1e-5f * std::max(ext, mag) + 1e-30f;
-
-    // device triangle records are written in leaf order below; an empty scene gets one node with two empty leaves
-    auto empty_leaf = [](BvhNode& nd, int c) {
-        float* q = nd.q;
-        if (c == 0) { q[0] = FLT_MAX; q[1] = -FLT_MAX; q[2] = FLT_MAX; q[3] = -FLT_MAX; q[8] = FLT_MAX; q[9] = -FLT_MAX; }
-        else        { q[4] = FLT_MAX; q[5] = -FLT_MAX; q[6] = FLT_MAX; q[7] = -FLT_MAX; q[10] = FLT_MAX; q[11] = -FLT_MAX; }
-        nd.child[c] = ~0;   // leaf, first 0, count 0
-    };
-    if (n == 0) {
-        BvhNode root{}; empty_leaf(root, 0); empty_leaf(root, 1); out.nodes.push_back(root);
-        out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-        return;
-    }
-
-    Builder b;
+    f.pad = 1e-5f * std::max(ext, mag) + 1e-30f;
+    if (n == 0) return;
+    Builder& b = f.b;
     b.tlo = tlo.data(); b.thi = thi.data(); b.maxLeaf = maxLeaf;
     b.order.resize(n);
     for (uint32_t t = 0; t < n; ++t) b.order[t] = t;
@@ -174,6 +165,31 @@ void build_bvh(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, 
         for (auto& th : pool) th.join();
     } else {
         b.build(0, 0, n);
+    }
+}
+
+void build_bvh(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, uint32_t maxLeaf, uint32_t threads,
+               BvhResult& out) {
+    auto t0 = std::chrono::steady_clock::now();
+    out = BvhResult();
+    if (maxLeaf < 1) maxLeaf = 1;
+    if (maxLeaf > 7) maxLeaf = 7;
+    Front front;
+    build_front(vertices, indices, n, maxLeaf, threads, front);
+    Builder& b = front.b;
+    out.pad = front.pad;
+
+    // device triangle records are written in leaf order below; an empty scene gets one node with two empty leaves
+    auto empty_leaf = [](BvhNode& nd, int c) {
+        float* q = nd.q;
+        if (c == 0) { q[0] = FLT_MAX; q[1] = -FLT_MAX; q[2] = FLT_MAX; q[3] = -FLT_MAX; q[8] = FLT_MAX; q[9] = -FLT_MAX; }
+        else        { q[4] = FLT_MAX; q[5] = -FLT_MAX; q[6] = FLT_MAX; q[7] = -FLT_MAX; q[10] = FLT_MAX; q[11] = -FLT_MAX; }
+        nd.child[c] = ~0;   // leaf, first 0, count 0
+    };
+    if (n == 0) {
+        BvhNode root{}; empty_leaf(root, 0); empty_leaf(root, 1); out.nodes.push_back(root);
+        out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        return;
     }
 
     // depth-first emission into device nodes; leaves become triangle runs
@@ -226,6 +242,281 @@ void build_bvh(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, 
     }
     out.sah_cost = float(sah);
     out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+
+// ---- 8-wide collapse (bvh8.h) ------------------------------------------------------------------------------------
+// Dynamic programme of Ylitie et al. 2017, section 3.1, over the binary tree: C(n, i) = cheapest way to present
+// subtree n as at most i children of a wide node; a child is either a leaf (<= 3 triangles, cost area * count * 0.3)
+// or another wide node (cost area * 1 + its 8 children).  Leaves of the binary tree are kept whole.
+namespace {
+
+constexpr float kCostNode = 1.0f, kCostPrim = 0.3f;
+constexpr uint32_t kMaxLeaf8 = 3;
+
+struct Collapse {
+    const Builder& b;
+    float invRootArea;
+    std::vector<float> C;        // [node][i-1], i = 1..7
+    std::vector<uint8_t> K;      // [node][0] = 1: single child is a leaf; [node][j-1], j = 2..8: left share of distribute(j)
+    std::vector<uint8_t> U;      // bit i: C(n,i) comes from distribute(i) rather than from C(n,i-1)
+    explicit Collapse(const Builder& bb) : b(bb) {
+        size_t m = bb.sparse.size();
+        C.assign(7 * m, 0.0f); K.assign(8 * m, 0); U.assign(m, 0);
+        invRootArea = 1.0f / std::max(bb.sparse[0].box.half_area(), 1e-30f);
+    }
+    bool leaf(uint32_t n) const { return b.sparse[n].leftCount == 0; }
+    uint32_t left(uint32_t n) const { return n + 1; }
+    uint32_t right(uint32_t n) const { return n + 2 * b.sparse[n].leftCount; }
+
+    void solve(uint32_t n) {
+        const BuildNode& nd = b.sparse[n];
+        const float A = nd.box.half_area() * invRootArea;
+        float* c = &C[7 * size_t(n)]; uint8_t* k = &K[8 * size_t(n)];
+        if (leaf(n)) {
+            for (int i = 0; i < 7; ++i) c[i] = A * float(nd.count) * kCostPrim;
+            k[0] = 1;
+            return;
+        }
+        const uint32_t l = left(n), r = right(n);
+        solve(l); solve(r);
+        const float* cl = &C[7 * size_t(l)]; const float* cr = &C[7 * size_t(r)];
+        float D[9];
+        for (int j = 2; j <= 8; ++j) {
+            float best = FLT_MAX; int bk = 1;
+            for (int kk = 1; kk < j; ++kk) {
+                if (kk > 7 || j - kk > 7) continue;
+                float v = cl[kk - 1] + cr[j - kk - 1];
+                if (v < best) { best = v; bk = kk; }
+            }
+            D[j] = best; k[j - 1] = uint8_t(bk);
+        }
+        const float cLeaf = nd.count <= kMaxLeaf8 ? A * float(nd.count) * kCostPrim : FLT_MAX;
+        const float cInner = D[8] + A * kCostNode;
+        c[0] = std::min(cLeaf, cInner); k[0] = cLeaf <= cInner ? 1 : 0;
+        uint8_t u = 0;
+        for (int i = 2; i <= 7; ++i) {
+            if (D[i] < c[i - 2]) { c[i - 1] = D[i]; u |= uint8_t(1u << i); } else c[i - 1] = c[i - 2];
+        }
+        U[n] = u;
+    }
+    bool is_leaf_child(uint32_t n) const { return leaf(n) || K[8 * size_t(n)] == 1; }
+
+    // binary-tree nodes that become the (<= budget) children of a wide node
+    void collect(uint32_t m, int budget, uint32_t* kids, int& count) const {
+        if (leaf(m) || budget == 1) { kids[count++] = m; return; }
+        while (budget >= 2 && !(U[m] & (1u << budget))) --budget;
+        if (budget == 1) { kids[count++] = m; return; }
+        int kk = K[8 * size_t(m) + budget - 1];
+        collect(left(m), kk, kids, count);
+        collect(right(m), budget - kk, kids, count);
+    }
+    void children_of(uint32_t n, uint32_t* kids, int& count) const {      // n is an inner wide node
+        count = 0;
+        int kk = K[8 * size_t(n) + 7];
+        collect(left(n), kk, kids, count);
+        collect(right(n), 8 - kk, kids, count);
+    }
+};
+
+}  // namespace
+
+void build_bvh8(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, uint32_t threads, Bvh8Result& out) {
+    auto t0 = std::chrono::steady_clock::now();
+    out = Bvh8Result();
+    Front front;
+    build_front(vertices, indices, n, kMaxLeaf8, threads, front);
+    const Builder& b = front.b;
+    const float pad = front.pad;
+    auto finish = [&] { out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+    if (n == 0) {                                   // one node without children: every ray misses
+        Bvh8Node root{}; root.e[0] = root.e[1] = root.e[2] = 127;
+        out.nodes.push_back(root); out.depth = 1; finish();
+        return;
+    }
+    Collapse col(b);
+    col.solve(0);
+    out.sah_cost = col.C[0];
+    out.tris.reserve(n);
+    out.nodes.reserve(size_t(n) / 4 + 16);
+
+    auto emit_tris = [&](const BuildNode& leaf) {
+        for (uint32_t k = leaf.first; k < leaf.first + leaf.count; ++k) {
+            uint32_t t = b.order[k];
+            const float* V0 = vertices[indices[3 * size_t(t)]].v; const float* V1 = vertices[indices[3 * size_t(t) + 1]].v;
+            const float* V2 = vertices[indices[3 * size_t(t) + 2]].v;
+            BvhTri r;
+            for (int a = 0; a < 3; ++a) { r.v2[a] = V2[a]; r.e1[a] = V0[a] - V2[a]; r.e2[a] = V1[a] - V2[a]; }
+            r.index = t; r.pad1 = 0.0f; r.pad2 = 0.0f;
+            out.tris.push_back(r);
+        }
+    };
+
+    struct Item { uint32_t bnode; uint32_t outIndex; uint32_t depth; bool wholeLeaf; };
+    std::deque<Item> queue;
+    out.nodes.push_back(Bvh8Node{});
+    queue.push_back(Item{0, 0, 1, col.is_leaf_child(0)});
+    while (!queue.empty()) {
+        Item it = queue.front(); queue.pop_front();
+        out.depth = std::max(out.depth, it.depth);
+        uint32_t kids[8]; int nk = 0;
+        if (it.wholeLeaf) { kids[0] = it.bnode; nk = 1; }          // only the root can be a bare leaf
+        else col.children_of(it.bnode, kids, nk);
+
+        // padded child boxes and their union
+        Box cb[8], nb; nb.reset();
+        for (int c = 0; c < nk; ++c) {
+            cb[c] = b.sparse[kids[c]].box;
+            for (int a = 0; a < 3; ++a) { cb[c].lo[a] -= pad; cb[c].hi[a] += pad; }
+            nb.grow(cb[c].lo, cb[c].hi);
+        }
+        // slot assignment: slot s (bit a set = +axis a) should hold the child lying furthest that way, so that
+        // visiting slots by descending (s ^ octInv) is roughly front to back for every ray octant
+        int slotOf[8]; bool slotUsed[8] = {}, kidDone[8] = {};
+        float score[8][8];
+        for (int c = 0; c < nk; ++c)
+            for (int s = 0; s < 8; ++s) {
+                float v = 0.0f;
+                for (int a = 0; a < 3; ++a) {
+                    float d = 0.5f * (cb[c].lo[a] + cb[c].hi[a]) - 0.5f * (nb.lo[a] + nb.hi[a]);
+                    v += ((s >> a) & 1) ? d : -d;
+                }
+                score[c][s] = v;
+            }
+        for (int r = 0; r < nk; ++r) {
+            int bc = -1, bs = -1; float bv = -FLT_MAX;
+            for (int c = 0; c < nk; ++c) if (!kidDone[c])
+                for (int s = 0; s < 8; ++s) if (!slotUsed[s] && (bc < 0 || score[c][s] > bv)) { bv = score[c][s]; bc = c; bs = s; }
+            slotOf[bc] = bs; kidDone[bc] = true; slotUsed[bs] = true;
+        }
+        int kidAt[8]; for (int s = 0; s < 8; ++s) kidAt[s] = -1;
+        for (int c = 0; c < nk; ++c) kidAt[slotOf[c]] = c;
+
+        Bvh8Node nd{};
+        for (int a = 0; a < 3; ++a) nd.p[a] = nb.lo[a];
+        // per-axis power-of-two grid step with 255 * step >= extent; planes rounded outwards
+        for (int a = 0; a < 3; ++a) {
+            double ext = double(nb.hi[a]) - double(nb.lo[a]);
+            int ex = 0;
+            std::frexp(std::max(ext, 1e-37) / 255.0, &ex);
+            for (;; ++ex) {
+                if (ex < -126) ex = -126;
+                const double step = std::ldexp(1.0, ex);
+                bool ok = true;
+                for (int c = 0; c < nk && ok; ++c) {
+                    double qh = std::ceil((double(cb[c].hi[a]) - double(nd.p[a])) / step);
+                    if (qh > 255.0) ok = false;
+                }
+                if (ok || ex >= 127) break;
+            }
+            nd.e[a] = uint8_t(ex + 127);
+            const double step = std::ldexp(1.0, ex);
+            for (int s = 0; s < 8; ++s) {
+                int c = kidAt[s];
+                if (c < 0) { nd.qlo[a][s] = 255; nd.qhi[a][s] = 0; continue; }      // empty slot: inverted box
+                double ql = std::floor((double(cb[c].lo[a]) - double(nd.p[a])) / step);
+                double qh = std::ceil((double(cb[c].hi[a]) - double(nd.p[a])) / step);
+                nd.qlo[a][s] = uint8_t(std::min(255.0, std::max(0.0, ql)));
+                nd.qhi[a][s] = uint8_t(std::min(255.0, std::max(0.0, qh)));
+            }
+        }
+        // children: inner ones get consecutive node indices in slot order, leaf triangles consecutive records
+        nd.childBase = uint32_t(out.nodes.size());
+        nd.triBase = uint32_t(out.tris.size());
+        uint32_t triOffset = 0;
+        for (int s = 0; s < 8; ++s) {
+            int c = kidAt[s];
+            if (c < 0) { nd.meta[s] = 0; continue; }
+            const BuildNode& ch = b.sparse[kids[c]];
+            if (col.is_leaf_child(kids[c])) {
+                nd.meta[s] = uint8_t((((1u << ch.count) - 1u) << 5) | triOffset);     // unary count, offset
+                emit_tris(ch);
+                triOffset += ch.count;
+            } else {
+                nd.imask |= uint8_t(1u << s);
+                nd.meta[s] = uint8_t(0x20u | (24u + uint32_t(s)));
+                uint32_t idx = uint32_t(out.nodes.size());
+                out.nodes.push_back(Bvh8Node{});
+                queue.push_back(Item{kids[c], idx, it.depth + 1, false});
+            }
+        }
+        out.nodes[it.outIndex] = nd;
+    }
+    finish();
+}
+
+// ---- host self-test of the wide tree (CPU test-suite; no rendering happens here) ---------------------------------
+namespace {
+struct HostHit { float t; uint32_t tri; };
+inline float hdot(const float* a, const float* b) { return std::fmaf(a[2], b[2], std::fmaf(a[1], b[1], a[0] * b[0])); }
+inline void hcross(const float* a, const float* b, float* r) {
+    r[0] = std::fmaf(a[1], b[2], -(a[2] * b[1])); r[1] = std::fmaf(a[2], b[0], -(a[0] * b[2])); r[2] = std::fmaf(a[0], b[1], -(a[1] * b[0]));
+}
+// same operation order as triangle_test in device_trace.cuh
+inline void host_triangle_test(const BvhTri& T, const float* o, const float* d, float tmin, float tmax, HostHit& best) {
+    float pv[3]; hcross(d, T.e2, pv);
+    float det = hdot(T.e1, pv);
+    float inv = 1.0f / det;
+    float s[3] = {o[0] - T.v2[0], o[1] - T.v2[1], o[2] - T.v2[2]};
+    float u = hdot(s, pv) * inv;
+    if (!(u >= 0.0f && u <= 1.0f)) return;
+    float q[3]; hcross(s, T.e1, q);
+    float v = hdot(d, q) * inv;
+    if (!(v >= 0.0f && u + v <= 1.0f)) return;
+    float t = hdot(T.e2, q) * inv;
+    if (!(t >= tmin && t <= tmax)) return;
+    if (t < best.t || (t == best.t && T.index < best.tri)) { best.t = t; best.tri = T.index; }
+}
+}  // namespace
+
+uint32_t bvh8_selftest(const Bvh8Result& bvh, const float* rays, uint32_t count, uint64_t* nodesVisited, uint64_t* trisTested) {
+    uint32_t bad = 0;
+    uint64_t nv = 0, tt = 0;
+    for (uint32_t i = 0; i < count; ++i) {
+        const float* o = rays + 8 * size_t(i); const float* d = o + 4;
+        const float tmin = o[3], tmax = d[3];
+        HostHit brute{tmax, 0xFFFFFFFFu};
+        for (const BvhTri& T : bvh.tris) host_triangle_test(T, o, d, tmin, tmax, brute);
+        // traversal, same state machine as device_trace8.cuh
+        HostHit best{tmax, 0xFFFFFFFFu};
+        const float tiny = 1e-30f;
+        Ray8 r;
+        r.ox = o[0]; r.oy = o[1]; r.oz = o[2];
+        r.invx = 1.0f / (std::fabs(d[0]) < tiny ? std::copysign(tiny, d[0]) : d[0]);
+        r.invy = 1.0f / (std::fabs(d[1]) < tiny ? std::copysign(tiny, d[1]) : d[1]);
+        r.invz = 1.0f / (std::fabs(d[2]) < tiny ? std::copysign(tiny, d[2]) : d[2]);
+        r.negx = std::signbit(d[0]); r.negy = std::signbit(d[1]); r.negz = std::signbit(d[2]);
+        r.octInv = 7u - (r.negx | (r.negy << 1) | (r.negz << 2));
+        uint32_t gx = 0, gy = 0x80000000u, tx = 0, ty = 0;       // node group (base, hits|imask), triangle group (base, hits)
+        uint32_t stack[2 * 64]; int sp = 0;
+        for (;;) {
+            if (gy & 0xff000000u) {
+                int bit = 31 - __builtin_clz(gy);
+                gy &= ~(1u << bit);
+                if (gy & 0xff000000u) { stack[2 * sp] = gx; stack[2 * sp + 1] = gy; ++sp; }
+                uint32_t slot = uint32_t(bit - 24) ^ r.octInv;
+                uint32_t rel = uint32_t(__builtin_popcount(gy & 0xffu & ((1u << slot) - 1u)));
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(&bvh.nodes[gx + rel]);
+                ++nv;
+                uint32_t hits = bvh8_hitmask(w, r, tmin, best.t);
+                gx = w[4]; gy = (hits & 0xff000000u) | (w[3] >> 24);
+                tx = w[5]; ty = hits & 0x00ffffffu;
+            }
+            while (ty) {
+                int k = __builtin_ctz(ty); ty &= ty - 1;
+                ++tt;
+                host_triangle_test(bvh.tris[tx + uint32_t(k)], o, d, tmin, tmax, best);
+            }
+            if (!(gy & 0xff000000u)) {
+                if (sp == 0) break;
+                --sp; gx = stack[2 * sp]; gy = stack[2 * sp + 1];
+            }
+        }
+        if (best.tri != brute.tri || !(best.t == brute.t)) ++bad;
+    }
+    if (nodesVisited) *nodesVisited = nv;
+    if (trisTested) *trisTested = tt;
+    return bad;
 }
 
 }  // namespace mrt

@@ -1,0 +1,160 @@
+// bvh8.h — 8-wide BVH with 8-bit quantised child boxes: 80-byte nodes (5 x 128-bit loads), built on the host by
+// collapsing the binned-SAH BVH2 of bvh.cpp, traversed by device_trace8.cuh.
+//
+// Replaces MPSTriangleAccelerationStructure / MPSRayIntersector (reference: renderer/Renderer.mm:456-469, 519-523,
+// 545-553; closed source).  Why 8-wide: on B200 the traversal is bound by the latency of dependent node fetches
+// (ncu, BVH2: long-scoreboard 16 of 23 stall cycles per issue, DRAM < 5 %); an 8-ary node cuts the dependent chain
+// ~3x and packs 8 child boxes in 80 B instead of 256 B, so far more of the tree stays in L1/L2.
+// Layout after Ylitie, Karras, Laine, "Efficient incoherent ray traversal on GPUs through compressed wide BVHs"
+// (HPG 2017): the node stores an origin p, a power-of-two scale per axis and, per child, 6 bytes of box planes
+// relative to p; children that are inner nodes are stored contiguously from childBase (slot order), triangles of
+// leaf children contiguously from triBase.  The boxes are CONSERVATIVE (quantised outwards around boxes that already
+// carry the builder's padding), so the result of a traversal is still min over all triangles of (t, index).
+#pragma once
+#include <cstdint>
+#include <vector>
+#include "bvh.h"
+
+#if defined(__CUDACC__)
+#define MRT_HD __host__ __device__ __forceinline__
+#else
+#include <cmath>
+#define MRT_HD inline
+#endif
+
+namespace mrt {
+
+struct Bvh8Node {
+    float p[3];             // origin of the quantisation grid (= lower corner of the node box)
+    uint8_t e[3];           // biased exponents: grid step on axis a = 2^(e[a]-127)
+    uint8_t imask;          // bit s set: child slot s is an inner node
+    uint32_t childBase;     // node index of the first inner child
+    uint32_t triBase;       // triangle record index of the first triangle of this node's leaf children
+    uint8_t meta[8];        // inner: 0x20 | (24 + slot); leaf: (unary triangle count << 5) | offset from triBase; empty: 0
+    uint8_t qlo[3][8];      // lower planes x,y,z per child slot
+    uint8_t qhi[3][8];      // upper planes
+};
+static_assert(sizeof(Bvh8Node) == 80, "wide node is 80 bytes");
+
+struct Bvh8Result {
+    std::vector<Bvh8Node> nodes;    // nodes[0] = root
+    std::vector<BvhTri> tris;       // 48-byte records (bvh.h), leaf order of THIS tree
+    uint32_t depth = 0;             // levels of wide nodes
+    float sah_cost = 0.0f;
+    double build_ms = 0.0;
+};
+
+// Collapse + quantise.  Same inputs as build_bvh; deterministic for any thread count.
+void build_bvh8(const mrt_vertex* vertices, const uint32_t* indices, uint32_t triangle_count, uint32_t threads, Bvh8Result& out);
+
+// Host-only check for the CPU test-suite: traverses `count` rays (8 floats each: origin, tmin, direction, tmax) through
+// the wide tree with the same node decode and state machine as the CUDA kernel and compares (t, triangle) with brute
+// force over all triangles.  Returns the number of rays that differ.
+uint32_t bvh8_selftest(const Bvh8Result& bvh, const float* rays, uint32_t count, uint64_t* nodesVisited, uint64_t* trisTested);
+
+// ---- node decode shared by the CUDA traversal and the host self-test --------------------------------------------
+// Ray constants for the quantised slab test.  inv* = 1/d with |d| clamped away from zero (box test only).
+struct Ray8 {
+    float ox, oy, oz;
+    float invx, invy, invz;
+    uint32_t negx, negy, negz;      // direction sign per axis (1 = negative)
+    uint32_t octInv;                // 7 - octant: traversal priority of slot s is s ^ octInv (highest first)
+};
+
+MRT_HD float mrt_bits_float(uint32_t b) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(b);
+#else
+    union { uint32_t u; float f; } c; c.u = b; return c.f;
+#endif
+}
+MRT_HD float mrt_fma(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+    return __fmaf_rn(a, b, c);
+#else
+    return std::fmaf(a, b, c);
+#endif
+}
+// min/max of finite values (FMNMX / FMNMX3 on sm_100a)
+MRT_HD float mrt_min3(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+    return fminf(fminf(a, b), c);
+#else
+    float m = a < b ? a : b; return m < c ? m : c;
+#endif
+}
+MRT_HD float mrt_max3(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+    return fmaxf(fmaxf(a, b), c);
+#else
+    float m = a > b ? a : b; return m > c ? m : c;
+#endif
+}
+// byte j of w as the float 32768 + byte: one PRMT builds the bit pattern 0x47 00 bb 00 (an int->float conversion
+// would go through the quarter-rate XU pipe: ncu showed it 65 % busy with 48 I2F.U8 per node)
+MRT_HD float mrt_plane(uint32_t w, int j) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404u | (uint32_t(j) << 4)));
+#else
+    return mrt_bits_float(0x47000000u | (((w >> (8 * j)) & 0xffu) << 8));
+#endif
+}
+MRT_HD uint32_t mrt_byte(uint32_t w, int j) {
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(w, 0u, 0x4440u | uint32_t(j));
+#else
+    return (w >> (8 * j)) & 0xffu;
+#endif
+}
+
+// Hit mask of one node for one ray: bits 24..31 = inner children hit, at bit 24 + (slot ^ octInv) (so the highest
+// set bit is the child to visit first); bits 0..23 = triangles of the leaf children hit, at their offset from
+// triBase.  w[] = the node as 20 32-bit words.  Non-strict comparison: boxes touching [tmin, tmax] count as hit.
+//
+// Plane k of a child lies at p + q*step; along the ray that is t = q*(step/d) + (p - o)/d.  With the byte decoded as
+// F = 32768 + q the same value is F*a + (b - 32768*a), a = step/d, b = (p - o)/d: one FFMA per plane.  The constant
+// c = b - 32768*a carries a rounding error of up to 2^-9 |a| (twice, once more when the guard is added), so entry
+// planes use c - 2^-7 |a| and exit planes c + 2^-7 |a|: the test stays conservative at a cost of < 1 % of a grid step.
+MRT_HD uint32_t bvh8_hitmask(const uint32_t* w, const Ray8& r, float tmin, float tmax) {
+    const uint32_t ew = w[3];
+    const float sx = mrt_bits_float((ew & 0xffu) << 23), sy = mrt_bits_float(((ew >> 8) & 0xffu) << 23),
+                sz = mrt_bits_float(((ew >> 16) & 0xffu) << 23);
+    const float ax = sx * r.invx, ay = sy * r.invy, az = sz * r.invz;
+    const float bx = (mrt_bits_float(w[0]) - r.ox) * r.invx, by = (mrt_bits_float(w[1]) - r.oy) * r.invy,
+                bz = (mrt_bits_float(w[2]) - r.oz) * r.invz;
+    const float cx = mrt_fma(-32768.0f, ax, bx), cy = mrt_fma(-32768.0f, ay, by), cz = mrt_fma(-32768.0f, az, bz);
+    const float gx = (ax < 0.0f ? -ax : ax) * 0.0078125f, gy = (ay < 0.0f ? -ay : ay) * 0.0078125f,
+                gz = (az < 0.0f ? -az : az) * 0.0078125f;
+    const float nxc = cx - gx, fxc = cx + gx, nyc = cy - gy, fyc = cy + gy, nzc = cz - gz, fzc = cz + gz;
+    const uint32_t oct4 = r.octInv * 0x01010101u;
+    uint32_t hit = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int h = 0; h < 2; ++h) {
+        // words: qlo x 8+h, y 10+h, z 12+h; qhi x 14+h, y 16+h, z 18+h
+        const uint32_t nx = r.negx ? w[14 + h] : w[8 + h], fx = r.negx ? w[8 + h] : w[14 + h];
+        const uint32_t ny = r.negy ? w[16 + h] : w[10 + h], fy = r.negy ? w[10 + h] : w[16 + h];
+        const uint32_t nz = r.negz ? w[18 + h] : w[12 + h], fz = r.negz ? w[12 + h] : w[18 + h];
+        // four children at a time: inner children (0x20 | 24 + slot) go to bit (24 + slot) ^ octInv, leaf children
+        // put their unary triangle count at their offset
+        const uint32_t meta4 = w[6 + h];
+        const uint32_t inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;           // bits 3 and 4 both set <=> index >= 24
+        const uint32_t innerMask4 = (inner4 >> 4) * 0xffu;
+        const uint32_t at4 = (meta4 ^ (oct4 & innerMask4)) & 0x1f1f1f1fu;
+        const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int j = 0; j < 4; ++j) {
+            const float t0x = mrt_fma(mrt_plane(nx, j), ax, nxc), t1x = mrt_fma(mrt_plane(fx, j), ax, fxc);
+            const float t0y = mrt_fma(mrt_plane(ny, j), ay, nyc), t1y = mrt_fma(mrt_plane(fy, j), ay, fyc);
+            const float t0z = mrt_fma(mrt_plane(nz, j), az, nzc), t1z = mrt_fma(mrt_plane(fz, j), az, fzc);
+            const float tn = mrt_max3(t0x, t0y, t0z), tf = mrt_min3(t1x, t1y, t1z);
+            if (tn <= tf && tn <= tmax && tf >= tmin) hit |= mrt_byte(bits4, j) << mrt_byte(at4, j);
+        }
+    }
+    return hit;
+}
+
+}  // namespace mrt

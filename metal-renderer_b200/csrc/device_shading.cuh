@@ -13,8 +13,10 @@ namespace mrt {
 
 // Scene as the kernels read it: 128-bit aligned records repacked from the ABI arrays at mrt_set_scene.
 struct DeviceScene {
-    const float4* nodes;        // 4 per BVH node (bvh.h)
-    const float4* tris;         // 3 per triangle, leaf order (bvh.h)
+    const float4* nodes;        // binary tree: 4 per node (bvh.h)
+    const float4* tris;         //              3 per triangle, leaf order of the binary tree
+    const float4* nodes8;       // 8-wide tree: 5 per node (bvh8.h)
+    const float4* tris8;        //              3 per triangle, leaf order of the wide tree
     const float4* shadeTris;    // 5 per triangle, original order: p0 p1 p2 n0 n1 n2 | materialIndex lightTriangleIndex
     const float4* materials;    // 2 per material: diffuse.rgb emissive.r | emissive.gb ior type
     const float4* lights;       // 6 per light triangle (count + 1 sentinel)

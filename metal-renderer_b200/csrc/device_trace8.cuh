@@ -1,0 +1,119 @@
+// device_trace8.cuh — persistent, vote-scheduled traversal of the 8-wide quantised BVH (bvh8.h) on sm_100a.
+//
+// Stands in for MPSRayIntersector nearest-hit (reference call sites renderer/Renderer.mm:464-469, 519-523, 545-553).
+// Same contract as trace_persistent in device_trace.cuh (IO policy, NEAREST / ANYHIT jobs, answer = min over all
+// triangles of (t, index) under triangle_test), different tree: one node fetch (5 x LDG.128) tests 8 children, so
+// the chain of dependent loads per ray is ~3x shorter than in the binary tree — the stall that dominated it.
+//
+// Per-lane state: node group G = (childBase, hits<<24 | imask) of inner children still to visit, triangle group
+// T = (triBase, 24-bit mask) of leaf triangles still to test, and a stack of node groups in local memory.
+// Every round the warp votes between a NODE step (pop the nearest child of G, fetch it, build new G/T) and a
+// TRIANGLE step (drain T); lanes that finish are refilled from the global work counter.
+#pragma once
+#include "bvh8.h"
+#include "device_trace.cuh"
+
+namespace mrt {
+
+#define MRT_STACK8 32          /* node groups; host checks the tree depth against it (api.cu) */
+
+template <class IO>
+__device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nodes8, const float4* __restrict__ tris,
+                                                  uint32_t total, unsigned int* head, uint32_t refillBelow, uint32_t leafMin,
+                                                  IO& io) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const float tiny = 1e-30f;
+    bool alive = false, exhausted = (total == 0);
+    uint32_t tag = 0, target = MRT_NO_HIT;
+    f3 o = mk3(0.f, 0.f, 0.f), d = o;
+    float tmin = 0.f, tmax = 0.f;
+    Ray8 r; r.ox = r.oy = r.oz = 0.f; r.invx = r.invy = r.invz = 0.f; r.negx = r.negy = r.negz = 0u; r.octInv = 0u;
+    HitRec best; best.t = 0.f; best.tri = MRT_NO_HIT; best.u = best.v = 0.f;
+    uint32_t gx = 0, gy = 0, tx = 0, ty = 0;
+    uint2 stack[MRT_STACK8];
+    int sp = 0;
+
+    for (;;) {
+        // ---- refill idle lanes until enough of the warp is busy (or the queue is empty) ----
+        unsigned am;
+        for (;;) {
+            am = __ballot_sync(0xffffffffu, alive);
+            if (exhausted || __popc(am) >= (int)refillBelow) break;
+            unsigned need = ~am;
+            uint32_t n = __popc(need), base = 0;
+            int leader = __ffs(need) - 1;
+            if ((int)lane == leader) base = atomicAdd(head, n);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!alive) {
+                uint32_t it = base + __popc(need & ((1u << lane) - 1u));
+                if (it < total) {
+                    TraceJob job;
+                    if (io.load(it, job)) {
+                        tag = job.tag; o = job.o; d = job.d; tmin = job.tmin; tmax = job.tmax; target = job.target;
+                        r.ox = o.x; r.oy = o.y; r.oz = o.z;
+                        r.invx = __fdiv_rn(1.0f, fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x);
+                        r.invy = __fdiv_rn(1.0f, fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y);
+                        r.invz = __fdiv_rn(1.0f, fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
+                        r.negx = __float_as_uint(d.x) >> 31; r.negy = __float_as_uint(d.y) >> 31; r.negz = __float_as_uint(d.z) >> 31;
+                        r.octInv = 7u - (r.negx | (r.negy << 1) | (r.negz << 2));
+                        best.t = tmax; best.tri = target; best.u = 0.0f; best.v = 0.0f;
+                        gx = 0; gy = 0x80000000u; tx = 0; ty = 0; sp = 0;       // group holding just the root
+                        alive = true;
+                    }
+                }
+            }
+            exhausted = base + n >= total;
+        }
+        if (am == 0) break;                               // queue empty and every lane idle
+
+        for (;;) {
+            const bool wantTri = alive && ty != 0;
+            const bool wantNode = alive && ty == 0;        // invariant: an alive lane with T empty has inner hits in G
+            const unsigned mN = __ballot_sync(0xffffffffu, wantNode);
+            const unsigned mT = __ballot_sync(0xffffffffu, wantTri);
+            if ((mN | mT) == 0) break;
+            if (mN != 0 && __popc(mT) < (int)leafMin) {
+                if (wantNode) {
+                    const int bit = 31 - __clz(gy);                             // nearest unvisited child in octant order
+                    gy &= ~(1u << bit);
+                    if (gy & 0xff000000u) stack[sp++] = make_uint2(gx, gy);
+                    const uint32_t slot = uint32_t(bit - 24) ^ r.octInv;
+                    const uint32_t rel = __popc(gy & 0xffu & ((1u << slot) - 1u));
+                    const float4* np = nodes8 + 5 * (size_t)(gx + rel);
+                    uint32_t w[20];
+                    {
+                        float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
+                        w[0] = __float_as_uint(q0.x); w[1] = __float_as_uint(q0.y); w[2] = __float_as_uint(q0.z); w[3] = __float_as_uint(q0.w);
+                        w[4] = __float_as_uint(q1.x); w[5] = __float_as_uint(q1.y); w[6] = __float_as_uint(q1.z); w[7] = __float_as_uint(q1.w);
+                        w[8] = __float_as_uint(q2.x); w[9] = __float_as_uint(q2.y); w[10] = __float_as_uint(q2.z); w[11] = __float_as_uint(q2.w);
+                        w[12] = __float_as_uint(q3.x); w[13] = __float_as_uint(q3.y); w[14] = __float_as_uint(q3.z); w[15] = __float_as_uint(q3.w);
+                        w[16] = __float_as_uint(q4.x); w[17] = __float_as_uint(q4.y); w[18] = __float_as_uint(q4.z); w[19] = __float_as_uint(q4.w);
+                    }
+                    const uint32_t hits = bvh8_hitmask(w, r, tmin, best.t);
+                    gx = w[4]; gy = (hits & 0xff000000u) | (w[3] >> 24);
+                    tx = w[5]; ty = hits & 0x00ffffffu;
+                    if (ty == 0 && !(gy & 0xff000000u)) {                       // nothing hit below: next group or done
+                        if (sp > 0) { uint2 e = stack[--sp]; gx = e.x; gy = e.y; }
+                        else { if (best.tri == MRT_NO_HIT) best.t = -1.0f; io.store(tag, target, best); alive = false; }
+                    }
+                }
+                continue;
+            }
+            if (wantTri) {                                  // one triangle per step: lanes with longer lists re-vote
+                const int k = __ffs(ty) - 1;
+                ty &= ty - 1u;
+                triangle_test(tris, tx + uint32_t(k), o, d, tmin, tmax, best);
+                if (target != MRT_NO_HIT && best.tri != target) {                // any-hit job: occluded, done
+                    ty = 0; io.store(tag, target, best); alive = false;
+                } else if (ty == 0 && !(gy & 0xff000000u)) {
+                    if (sp > 0) { uint2 e = stack[--sp]; gx = e.x; gy = e.y; }
+                    else { if (best.tri == MRT_NO_HIT) best.t = -1.0f; io.store(tag, target, best); alive = false; }
+                }
+            }
+            const unsigned a2 = __ballot_sync(0xffffffffu, alive);
+            if (a2 == 0 || (!exhausted && __popc(a2) < (int)refillBelow)) break;
+        }
+    }
+}
+
+}  // namespace mrt

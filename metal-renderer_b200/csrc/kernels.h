@@ -60,11 +60,13 @@ struct WfBuffers {
     uint32_t* queueShadow[2];
     unsigned int* counts;    // [parity][0 ext, 1 shadow]
     unsigned int* heads;     // [parity] work counter of the persistent trace kernel
-    const uint32_t* triSlot; // original triangle index -> leaf-order record (bvh.h)
+    const uint32_t* triSlot; // original triangle index -> record in triRecords
+    const float4* triRecords;// the triangle records the trace kernel uses (wide or binary tree order)
     uint32_t slots;          // tilesX * tilesY * 32
 };
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays);
 void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave);
+bool trace_uses_wide_bvh();   // MRT_BVH_WIDTH=2 selects the binary tree (A/B runs); default 8
 int wf_kernel_info(int* traceRegs, int* traceBlocksPerSM, int* shadeRegs);
 
 // fused megakernel: whole frames, ray state in registers

@@ -16,6 +16,7 @@
 #include <cstdlib>
 #include "kernels.h"
 #include "device_trace.cuh"
+#include "device_trace8.cuh"
 
 namespace mrt {
 
@@ -48,13 +49,14 @@ struct StridedIO {
     }
 };
 
-template <int MINB>
+template <int MINB, int WIDE>
 __global__ void __launch_bounds__(128, MINB) k_intersect_persistent(DeviceScene S, const char* __restrict__ rays, uint32_t stride,
                                                                     uint32_t count, mrt_intersection* __restrict__ out, Grid2D g,
                                                                     bool useGrid, bool vec, unsigned long long* liveCounter,
                                                                     unsigned int* head, uint32_t refillBelow, uint32_t leafMin) {
     StridedIO io; io.rays = rays; io.stride = stride; io.out = out; io.g = g; io.useGrid = useGrid; io.vec = vec; io.live = 0;
-    trace_persistent(S.nodes, S.tris, count, head, refillBelow, leafMin, io);
+    if (WIDE) trace_persistent8(S.nodes8, S.tris8, count, head, refillBelow, leafMin, io);
+    else trace_persistent(S.nodes, S.tris, count, head, refillBelow, leafMin, io);
     if (liveCounter) {
         uint32_t n = __reduce_add_sync(0xffffffffu, io.live);
         if ((threadIdx.x & 31) == 0 && n) atomicAdd(liveCounter, (unsigned long long)n);
@@ -87,7 +89,7 @@ struct WfIO {
     }
 };
 
-template <int MINB>
+template <int MINB, int WIDE>
 __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers b, uint32_t parity, uint32_t refillBelow,
                                                         uint32_t leafMin, unsigned long long* counters) {
     const uint32_t nExt = b.counts[2 * parity], nShadow = b.counts[2 * parity + 1];
@@ -98,7 +100,8 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     }
     WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
-    trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
+    if (WIDE) trace_persistent8(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
+    else trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
 }
 
 // ---- k_wf_shade: resolve -> intersectionHandler -> accumulate/regenerate, queue compaction ----------------------
@@ -150,7 +153,7 @@ __global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, u
                         liveShadow = 1;
                         // the light-sampling ray can only count if it reaches its target at t >= DISTANCE_EPSILON
                         HitRec tg; tg.t = INFINITY; tg.tri = MRT_NO_HIT; tg.u = tg.v = 0.0f;
-                        triangle_test(P.S.tris, __ldg(b.triSlot + sh.targetIndex), st.origin, sh.direction, 0.0f, INFINITY, tg);
+                        triangle_test(b.triRecords, __ldg(b.triSlot + sh.targetIndex), st.origin, sh.direction, 0.0f, INFINITY, tg);
                         if (tg.tri == sh.targetIndex && tg.t >= MRT_DISTANCE_EPSILON) {
                             pushS = true; pending = 1;
                             b.S0[slot] = make_float4(sh.direction.x, sh.direction.y, sh.direction.z, tg.t);
@@ -214,9 +217,11 @@ static int device_sms() {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     return n > 0 ? n : 148;
 }
-struct TraceTuning { int minb, refill, leafMin; };
+struct TraceTuning { int minb, refill, leafMin, wide; };
 static TraceTuning trace_tuning() {
-    static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", 10), env_int("MRT_TRACE_REFILL", 24), env_int("MRT_TRACE_LEAFMIN", 8) };
+    static const int wide = env_int("MRT_BVH_WIDTH", 8) == 8 ? 1 : 0;
+    static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", wide ? 8 : 10), env_int("MRT_TRACE_REFILL", 16),
+                                   env_int("MRT_TRACE_LEAFMIN", 8), wide };
     return t;
 }
 
@@ -231,11 +236,15 @@ void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const voi
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
     const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin));
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); uint32_t need = (warpsNeeded + 3u) / 4u; return need < cap ? need : cap; };
-    if (t.minb >= 16)      k_intersect_persistent<16><<<blocks(16), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
-    else if (t.minb >= 12) k_intersect_persistent<12><<<blocks(12), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
-    else if (t.minb >= 10) k_intersect_persistent<10><<<blocks(10), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
-    else if (t.minb >= 8)  k_intersect_persistent<8><<<blocks(8), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
-    else                   k_intersect_persistent<6><<<blocks(6), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin);
+#define MRT_LAUNCH_ISECT(MB, WD) k_intersect_persistent<MB, WD><<<blocks(MB), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin)
+    if (t.wide) {
+        if (t.minb >= 12) MRT_LAUNCH_ISECT(12, 1); else if (t.minb >= 10) MRT_LAUNCH_ISECT(10, 1);
+        else if (t.minb >= 8) MRT_LAUNCH_ISECT(8, 1); else if (t.minb >= 6) MRT_LAUNCH_ISECT(6, 1); else MRT_LAUNCH_ISECT(5, 1);
+    } else {
+        if (t.minb >= 12) MRT_LAUNCH_ISECT(12, 0); else if (t.minb >= 10) MRT_LAUNCH_ISECT(10, 0);
+        else if (t.minb >= 8) MRT_LAUNCH_ISECT(8, 0); else if (t.minb >= 6) MRT_LAUNCH_ISECT(6, 0); else MRT_LAUNCH_ISECT(5, 0);
+    }
+#undef MRT_LAUNCH_ISECT
 }
 
 void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave) {
@@ -245,11 +254,15 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     const uint32_t parity = wave & 1u;
     const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
-    if (t.minb >= 16)      k_wf_trace<16><<<blocks(16), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
-    else if (t.minb >= 12) k_wf_trace<12><<<blocks(12), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
-    else if (t.minb >= 10) k_wf_trace<10><<<blocks(10), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
-    else if (t.minb >= 8)  k_wf_trace<8><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
-    else                   k_wf_trace<6><<<blocks(6), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters);
+#define MRT_LAUNCH_TRACE(MB, WD) k_wf_trace<MB, WD><<<blocks(MB), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters)
+    if (t.wide) {
+        if (t.minb >= 12) MRT_LAUNCH_TRACE(12, 1); else if (t.minb >= 10) MRT_LAUNCH_TRACE(10, 1);
+        else if (t.minb >= 8) MRT_LAUNCH_TRACE(8, 1); else if (t.minb >= 6) MRT_LAUNCH_TRACE(6, 1); else MRT_LAUNCH_TRACE(5, 1);
+    } else {
+        if (t.minb >= 12) MRT_LAUNCH_TRACE(12, 0); else if (t.minb >= 10) MRT_LAUNCH_TRACE(10, 0);
+        else if (t.minb >= 8) MRT_LAUNCH_TRACE(8, 0); else if (t.minb >= 6) MRT_LAUNCH_TRACE(6, 0); else MRT_LAUNCH_TRACE(5, 0);
+    }
+#undef MRT_LAUNCH_TRACE
 }
 
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays) {
@@ -260,15 +273,17 @@ void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     else           k_wf_shade<false><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u);
 }
 
+bool trace_uses_wide_bvh() { return trace_tuning().wide != 0; }
+
 int wf_kernel_info(int* traceRegs, int* traceBlocksPerSM, int* shadeRegs) {
     cudaFuncAttributes a;
-    cudaError_t e = cudaFuncGetAttributes(&a, k_wf_trace<8>);
+    cudaError_t e = cudaFuncGetAttributes(&a, k_wf_trace<8, 1>);
     if (e != cudaSuccess) return (int)e;
     *traceRegs = a.numRegs;
     e = cudaFuncGetAttributes(&a, k_wf_shade<true>);
     if (e != cudaSuccess) return (int)e;
     *shadeRegs = a.numRegs;
-    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(traceBlocksPerSM, k_wf_trace<8>, 128, 0);
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(traceBlocksPerSM, k_wf_trace<8, 1>, 128, 0);
 }
 
 }  // namespace mrt

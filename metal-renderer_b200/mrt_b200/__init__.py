@@ -3,6 +3,6 @@ from ._lib import (ACCUM_MEAN, ACCUM_REPLACE, ACCUM_SUM, BUF_IMAGE, BUF_INTERSEC
                    INTERSECTION, LIGHT_RAY, LIGHT_TRIANGLE, MATERIAL, NOISE_TILE_FLOATS, NOT_A_LIGHT, PIPELINE_AUTO,
                    PIPELINE_MEGAKERNEL, PIPELINE_STAGED, PIPELINE_WAVEFRONT, RAY, TRIANGLE_REFERENCE, VERTEX, MrtError, lib)
 from .renderer import Renderer
-from .scene import PROCEDURAL_SCENES, Scene, noise_tile, noise_tiles
+from .scene import PROCEDURAL_SCENES, Scene, bvh_selftest, noise_tile, noise_tiles
 
 __all__ = [n for n in dir() if not n.startswith("_")]

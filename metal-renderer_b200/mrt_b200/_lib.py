@@ -49,7 +49,7 @@ class Stats(C.Structure):
                 ("frames_rendered", C.c_uint64), ("nodes_visited", C.c_uint64), ("triangles_tested", C.c_uint64),
                 ("last_render_ms", C.c_float), ("bvh_nodes", C.c_uint32), ("bvh_depth", C.c_uint32),
                 ("bvh_sah_cost", C.c_float), ("bvh_build_ms", C.c_float), ("last_kernel_ms", C.c_float),
-                ("reserved", C.c_uint32 * 4)]
+                ("bvh8_nodes", C.c_uint32), ("bvh8_depth", C.c_uint32), ("reserved", C.c_uint32 * 2)]
 
 
 class SceneView(C.Structure):
@@ -58,6 +58,12 @@ class SceneView(C.Structure):
                 ("references", C.c_void_p),
                 ("materials", C.c_void_p), ("material_count", C.c_uint32),
                 ("lights", C.c_void_p), ("light_count", C.c_uint32)]
+
+
+class BvhReport(C.Structure):
+    _fields_ = [("nodes", C.c_uint32), ("depth", C.c_uint32), ("triangles", C.c_uint32), ("mismatches", C.c_uint32),
+                ("sah_cost", C.c_float), ("build_ms", C.c_float), ("nodes_per_ray", C.c_float),
+                ("triangles_per_ray", C.c_float)]
 
 
 class MrtError(RuntimeError):
@@ -105,6 +111,7 @@ SIGNATURES = {
     "mrt_scene_load_obj": (C.c_int, [C.c_char_p, C.POINTER(_P)]),
     "mrt_scene_get": (C.c_int, [_P, C.POINTER(SceneView)]),
     "mrt_scene_destroy": (None, [_P]),
+    "mrt_bvh_selftest": (C.c_int, [_P, _U32, _U64, C.POINTER(BvhReport)]),
     "mrt_noise_fill": (None, [_U64, _U32, _P]),
 }
 

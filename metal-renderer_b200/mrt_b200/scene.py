@@ -72,3 +72,19 @@ def noise_tiles(seed, first_frame, count, out=None):
     for k in range(count):
         L.lib().mrt_noise_fill(int(seed), int(first_frame + k), L.ptr(tiles[k]))
     return tiles
+
+
+def bvh_selftest(name, seed=0, n_rays=2000, ray_seed=1):
+    """Host-only: build the 8-wide BVH of a procedural scene (or an .obj path) and check a host copy of the traversal
+    against brute force.  Returns a dict (mismatches must be 0)."""
+    handle = C.c_void_p()
+    if str(name).endswith(".obj"):
+        L.check(L.lib().mrt_scene_load_obj(str(name).encode(), C.byref(handle)))
+    else:
+        L.check(L.lib().mrt_scene_create_procedural(str(name).encode(), int(seed), C.byref(handle)))
+    rep = L.BvhReport()
+    try:
+        L.check(L.lib().mrt_bvh_selftest(handle, int(n_rays), int(ray_seed), C.byref(rep)))
+    finally:
+        L.lib().mrt_scene_destroy(handle)
+    return {n: getattr(rep, n) for n, _ in L.BvhReport._fields_}
