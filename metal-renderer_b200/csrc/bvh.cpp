@@ -487,20 +487,22 @@ uint32_t bvh8_selftest(const Bvh8Result& bvh, const float* rays, uint32_t count,
         r.invz = 1.0f / (std::fabs(d[2]) < tiny ? std::copysign(tiny, d[2]) : d[2]);
         r.negx = std::signbit(d[0]); r.negy = std::signbit(d[1]); r.negz = std::signbit(d[2]);
         r.octInv = 7u - (r.negx | (r.negy << 1) | (r.negz << 2));
-        uint32_t gx = 0, gy = 0x80000000u, tx = 0, ty = 0;       // node group (base, hits|imask), triangle group (base, hits)
+        r.magic = 0x47000000u;
+        uint32_t gx = 0, gy = 0x01000000u, tx = 0, ty = 0;       // node group (base, slot hits << 24 | imask), triangle group
         uint32_t stack[2 * 64]; int sp = 0;
         for (;;) {
             if (gy & 0xff000000u) {
-                int bit = 31 - __builtin_clz(gy);
-                gy &= ~(1u << bit);
+                uint32_t pr = mrt_perm8(gy >> 24, r.octInv);
+                uint32_t slot = uint32_t(31 - __builtin_clz(pr)) ^ r.octInv;
+                gy &= ~(0x01000000u << slot);
                 if (gy & 0xff000000u) { stack[2 * sp] = gx; stack[2 * sp + 1] = gy; ++sp; }
-                uint32_t slot = uint32_t(bit - 24) ^ r.octInv;
                 uint32_t rel = uint32_t(__builtin_popcount(gy & 0xffu & ((1u << slot) - 1u)));
                 const uint32_t* w = reinterpret_cast<const uint32_t*>(&bvh.nodes[gx + rel]);
                 ++nv;
-                uint32_t hits = bvh8_hitmask(w, r, tmin, best.t);
-                gx = w[4]; gy = (hits & 0xff000000u) | (w[3] >> 24);
-                tx = w[5]; ty = hits & 0x00ffffffu;
+                uint32_t hs = bvh8_hit_slots(w, r, tmin, best.t);
+                uint32_t imask = w[3] >> 24;
+                gx = w[4]; gy = ((hs & imask) << 24) | imask;
+                tx = w[5]; ty = bvh8_triangle_mask(w[6], w[7], hs & ~imask);
             }
             while (ty) {
                 int k = __builtin_ctz(ty); ty &= ty - 1;

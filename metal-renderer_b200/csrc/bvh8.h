@@ -59,6 +59,7 @@ struct Ray8 {
     float invx, invy, invz;
     uint32_t negx, negy, negz;      // direction sign per axis (1 = negative)
     uint32_t octInv;                // 7 - octant: traversal priority of slot s is s ^ octInv (highest first)
+    uint32_t magic;                 // 0x47000000, kept in a REGISTER so that PRMT takes its selector as an immediate
 };
 
 MRT_HD float mrt_bits_float(uint32_t b) {
@@ -92,30 +93,37 @@ MRT_HD float mrt_max3(float a, float b, float c) {
 }
 // byte j of w as the float 32768 + byte: one PRMT builds the bit pattern 0x47 00 bb 00 (an int->float conversion
 // would go through the quarter-rate XU pipe: ncu showed it 65 % busy with 48 I2F.U8 per node)
-MRT_HD float mrt_plane(uint32_t w, int j) {
+MRT_HD float mrt_plane(uint32_t w, int j, uint32_t magic) {
 #if defined(__CUDA_ARCH__)
-    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404u | (uint32_t(j) << 4)));
+    return __uint_as_float(__byte_perm(w, magic, 0x7404u | (uint32_t(j) << 4)));
 #else
-    return mrt_bits_float(0x47000000u | (((w >> (8 * j)) & 0xffu) << 8));
+    return mrt_bits_float(magic | (((w >> (8 * j)) & 0xffu) << 8));
 #endif
 }
-MRT_HD uint32_t mrt_byte(uint32_t w, int j) {
+// byte s (0..7) of the 8-byte pair (lo, hi)
+MRT_HD uint32_t mrt_byte8(uint32_t lo, uint32_t hi, uint32_t s) {
 #if defined(__CUDA_ARCH__)
-    return __byte_perm(w, 0u, 0x4440u | uint32_t(j));
+    return __byte_perm(lo, hi, 0x4440u | s) & 0xffu;
 #else
-    return (w >> (8 * j)) & 0xffu;
+    return ((s < 4 ? lo : hi) >> (8 * (s & 3u))) & 0xffu;
 #endif
+}
+// x with bit i moved to bit i ^ c (c in 0..7): the order in which a ray of octant 7 - c wants to visit child slots
+MRT_HD uint32_t mrt_perm8(uint32_t x, uint32_t c) {
+    if (c & 1u) x = ((x & 0xaau) >> 1) | ((x & 0x55u) << 1);
+    if (c & 2u) x = ((x & 0xccu) >> 2) | ((x & 0x33u) << 2);
+    if (c & 4u) x = ((x & 0xf0u) >> 4) | ((x & 0x0fu) << 4);
+    return x;
 }
 
-// Hit mask of one node for one ray: bits 24..31 = inner children hit, at bit 24 + (slot ^ octInv) (so the highest
-// set bit is the child to visit first); bits 0..23 = triangles of the leaf children hit, at their offset from
-// triBase.  w[] = the node as 20 32-bit words.  Non-strict comparison: boxes touching [tmin, tmax] count as hit.
+// Children of one node hit by one ray, as a mask over child SLOTS (bit s = slot s).  w[] = the node as 20 32-bit
+// words.  Non-strict comparison: boxes touching [tmin, tmax] count as hit.  Empty slots carry an inverted box.
 //
 // Plane k of a child lies at p + q*step; along the ray that is t = q*(step/d) + (p - o)/d.  With the byte decoded as
 // F = 32768 + q the same value is F*a + (b - 32768*a), a = step/d, b = (p - o)/d: one FFMA per plane.  The constant
 // c = b - 32768*a carries a rounding error of up to 2^-9 |a| (twice, once more when the guard is added), so entry
 // planes use c - 2^-7 |a| and exit planes c + 2^-7 |a|: the test stays conservative at a cost of < 1 % of a grid step.
-MRT_HD uint32_t bvh8_hitmask(const uint32_t* w, const Ray8& r, float tmin, float tmax) {
+MRT_HD uint32_t bvh8_hit_slots(const uint32_t* w, const Ray8& r, float tmin, float tmax) {
     const uint32_t ew = w[3];
     const float sx = mrt_bits_float((ew & 0xffu) << 23), sy = mrt_bits_float(((ew >> 8) & 0xffu) << 23),
                 sz = mrt_bits_float(((ew >> 16) & 0xffu) << 23);
@@ -126,7 +134,7 @@ MRT_HD uint32_t bvh8_hitmask(const uint32_t* w, const Ray8& r, float tmin, float
     const float gx = (ax < 0.0f ? -ax : ax) * 0.0078125f, gy = (ay < 0.0f ? -ay : ay) * 0.0078125f,
                 gz = (az < 0.0f ? -az : az) * 0.0078125f;
     const float nxc = cx - gx, fxc = cx + gx, nyc = cy - gy, fyc = cy + gy, nzc = cz - gz, fzc = cz + gz;
-    const uint32_t oct4 = r.octInv * 0x01010101u;
+    const uint32_t k = r.magic;
     uint32_t hit = 0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -136,25 +144,34 @@ MRT_HD uint32_t bvh8_hitmask(const uint32_t* w, const Ray8& r, float tmin, float
         const uint32_t nx = r.negx ? w[14 + h] : w[8 + h], fx = r.negx ? w[8 + h] : w[14 + h];
         const uint32_t ny = r.negy ? w[16 + h] : w[10 + h], fy = r.negy ? w[10 + h] : w[16 + h];
         const uint32_t nz = r.negz ? w[18 + h] : w[12 + h], fz = r.negz ? w[12 + h] : w[18 + h];
-        // four children at a time: inner children (0x20 | 24 + slot) go to bit (24 + slot) ^ octInv, leaf children
-        // put their unary triangle count at their offset
-        const uint32_t meta4 = w[6 + h];
-        const uint32_t inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;           // bits 3 and 4 both set <=> index >= 24
-        const uint32_t innerMask4 = (inner4 >> 4) * 0xffu;
-        const uint32_t at4 = (meta4 ^ (oct4 & innerMask4)) & 0x1f1f1f1fu;
-        const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
         for (int j = 0; j < 4; ++j) {
-            const float t0x = mrt_fma(mrt_plane(nx, j), ax, nxc), t1x = mrt_fma(mrt_plane(fx, j), ax, fxc);
-            const float t0y = mrt_fma(mrt_plane(ny, j), ay, nyc), t1y = mrt_fma(mrt_plane(fy, j), ay, fyc);
-            const float t0z = mrt_fma(mrt_plane(nz, j), az, nzc), t1z = mrt_fma(mrt_plane(fz, j), az, fzc);
+            const float t0x = mrt_fma(mrt_plane(nx, j, k), ax, nxc), t1x = mrt_fma(mrt_plane(fx, j, k), ax, fxc);
+            const float t0y = mrt_fma(mrt_plane(ny, j, k), ay, nyc), t1y = mrt_fma(mrt_plane(fy, j, k), ay, fyc);
+            const float t0z = mrt_fma(mrt_plane(nz, j, k), az, nzc), t1z = mrt_fma(mrt_plane(fz, j, k), az, fzc);
             const float tn = mrt_max3(t0x, t0y, t0z), tf = mrt_min3(t1x, t1y, t1z);
-            if (tn <= tf && tn <= tmax && tf >= tmin) hit |= mrt_byte(bits4, j) << mrt_byte(at4, j);
+            if (tn <= tf && tn <= tmax && tf >= tmin) hit |= 1u << (4 * h + j);
         }
     }
     return hit;
+}
+
+// Triangle mask (bit = offset from triBase) of the leaf children in `leafSlots`; meta bytes = w[6], w[7].
+MRT_HD uint32_t bvh8_triangle_mask(uint32_t meta0, uint32_t meta1, uint32_t leafSlots) {
+    uint32_t m = 0;
+    while (leafSlots) {
+#if defined(__CUDA_ARCH__)
+        const uint32_t s = uint32_t(__ffs(leafSlots)) - 1u;
+#else
+        const uint32_t s = uint32_t(__builtin_ctz(leafSlots));
+#endif
+        leafSlots &= leafSlots - 1u;
+        const uint32_t b = mrt_byte8(meta0, meta1, s);
+        m |= (b >> 5) << (b & 0x1fu);
+    }
+    return m;
 }
 
 }  // namespace mrt

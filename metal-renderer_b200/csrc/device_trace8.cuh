@@ -20,14 +20,20 @@ namespace mrt {
 template <class IO>
 __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nodes8, const float4* __restrict__ tris,
                                                   uint32_t total, unsigned int* head, uint32_t refillBelow, uint32_t leafMin,
-                                                  IO& io) {
+                                                  uint32_t magic, IO& io) {
+    // magic = 0x47000000 arrives as a kernel PARAMETER: were it a literal, ptxas would make it PRMT's immediate and
+    // spend an extra move per plane on the byte selector instead (bvh8.h: mrt_plane)
+    // visiting order of child slots per ray octant: lut[c][x] = x with bit i moved to bit i ^ c
+    __shared__ uint8_t orderLut[8 * 256];
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) orderLut[i] = (uint8_t)mrt_perm8(i & 0xffu, i >> 8);
+    __syncthreads();
     const uint32_t lane = threadIdx.x & 31u;
     const float tiny = 1e-30f;
     bool alive = false, exhausted = (total == 0);
     uint32_t tag = 0, target = MRT_NO_HIT;
     f3 o = mk3(0.f, 0.f, 0.f), d = o;
     float tmin = 0.f, tmax = 0.f;
-    Ray8 r; r.ox = r.oy = r.oz = 0.f; r.invx = r.invy = r.invz = 0.f; r.negx = r.negy = r.negz = 0u; r.octInv = 0u;
+    Ray8 r; r.ox = r.oy = r.oz = 0.f; r.invx = r.invy = r.invz = 0.f; r.negx = r.negy = r.negz = 0u; r.octInv = 0u; r.magic = magic;
     HitRec best; best.t = 0.f; best.tri = MRT_NO_HIT; best.u = best.v = 0.f;
     uint32_t gx = 0, gy = 0, tx = 0, ty = 0;
     uint2 stack[MRT_STACK8];
@@ -57,7 +63,7 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
                         r.negx = __float_as_uint(d.x) >> 31; r.negy = __float_as_uint(d.y) >> 31; r.negz = __float_as_uint(d.z) >> 31;
                         r.octInv = 7u - (r.negx | (r.negy << 1) | (r.negz << 2));
                         best.t = tmax; best.tri = target; best.u = 0.0f; best.v = 0.0f;
-                        gx = 0; gy = 0x80000000u; tx = 0; ty = 0; sp = 0;       // group holding just the root
+                        gx = 0; gy = 0x01000000u; tx = 0; ty = 0; sp = 0;       // group holding just the root (as slot 0)
                         alive = true;
                     }
                 }
@@ -74,10 +80,11 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
             if ((mN | mT) == 0) break;
             if (mN != 0 && __popc(mT) < (int)leafMin) {
                 if (wantNode) {
-                    const int bit = 31 - __clz(gy);                             // nearest unvisited child in octant order
-                    gy &= ~(1u << bit);
+                    // nearest unvisited inner child in octant order (G keeps its hits in slot space)
+                    const uint32_t pr = orderLut[(r.octInv << 8) | (gy >> 24)];
+                    const uint32_t slot = uint32_t(31 - __clz(pr)) ^ r.octInv;
+                    gy &= ~(0x01000000u << slot);
                     if (gy & 0xff000000u) stack[sp++] = make_uint2(gx, gy);
-                    const uint32_t slot = uint32_t(bit - 24) ^ r.octInv;
                     const uint32_t rel = __popc(gy & 0xffu & ((1u << slot) - 1u));
                     const float4* np = nodes8 + 5 * (size_t)(gx + rel);
                     uint32_t w[20];
@@ -89,9 +96,10 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
                         w[12] = __float_as_uint(q3.x); w[13] = __float_as_uint(q3.y); w[14] = __float_as_uint(q3.z); w[15] = __float_as_uint(q3.w);
                         w[16] = __float_as_uint(q4.x); w[17] = __float_as_uint(q4.y); w[18] = __float_as_uint(q4.z); w[19] = __float_as_uint(q4.w);
                     }
-                    const uint32_t hits = bvh8_hitmask(w, r, tmin, best.t);
-                    gx = w[4]; gy = (hits & 0xff000000u) | (w[3] >> 24);
-                    tx = w[5]; ty = hits & 0x00ffffffu;
+                    const uint32_t hs = bvh8_hit_slots(w, r, tmin, best.t);
+                    const uint32_t imask = w[3] >> 24;
+                    gx = w[4]; gy = ((hs & imask) << 24) | imask;
+                    tx = w[5]; ty = bvh8_triangle_mask(w[6], w[7], hs & ~imask);
                     if (ty == 0 && !(gy & 0xff000000u)) {                       // nothing hit below: next group or done
                         if (sp > 0) { uint2 e = stack[--sp]; gx = e.x; gy = e.y; }
                         else { if (best.tri == MRT_NO_HIT) best.t = -1.0f; io.store(tag, target, best); alive = false; }

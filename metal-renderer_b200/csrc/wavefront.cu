@@ -53,9 +53,9 @@ template <int MINB, int WIDE>
 __global__ void __launch_bounds__(128, MINB) k_intersect_persistent(DeviceScene S, const char* __restrict__ rays, uint32_t stride,
                                                                     uint32_t count, mrt_intersection* __restrict__ out, Grid2D g,
                                                                     bool useGrid, bool vec, unsigned long long* liveCounter,
-                                                                    unsigned int* head, uint32_t refillBelow, uint32_t leafMin) {
+                                                                    unsigned int* head, uint32_t refillBelow, uint32_t leafMin, uint32_t magic) {
     StridedIO io; io.rays = rays; io.stride = stride; io.out = out; io.g = g; io.useGrid = useGrid; io.vec = vec; io.live = 0;
-    if (WIDE) trace_persistent8(S.nodes8, S.tris8, count, head, refillBelow, leafMin, io);
+    if (WIDE) trace_persistent8(S.nodes8, S.tris8, count, head, refillBelow, leafMin, magic, io);
     else trace_persistent(S.nodes, S.tris, count, head, refillBelow, leafMin, io);
     if (liveCounter) {
         uint32_t n = __reduce_add_sync(0xffffffffu, io.live);
@@ -91,7 +91,7 @@ struct WfIO {
 
 template <int MINB, int WIDE>
 __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers b, uint32_t parity, uint32_t refillBelow,
-                                                        uint32_t leafMin, unsigned long long* counters) {
+                                                        uint32_t leafMin, uint32_t magic, unsigned long long* counters) {
     const uint32_t nExt = b.counts[2 * parity], nShadow = b.counts[2 * parity + 1];
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // the other queue pair was consumed by the previous wave's trace; clear it for the shade that follows us
@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     }
     WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
-    if (WIDE) trace_persistent8(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
+    if (WIDE) trace_persistent8(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic, io);
     else trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
 }
 
@@ -220,7 +220,7 @@ static int device_sms() {
 struct TraceTuning { int minb, refill, leafMin, wide; };
 static TraceTuning trace_tuning() {
     static const int wide = env_int("MRT_BVH_WIDTH", 8) == 8 ? 1 : 0;
-    static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", wide ? 8 : 10), env_int("MRT_TRACE_REFILL", 16),
+    static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", wide ? 8 : 10), env_int("MRT_TRACE_REFILL", 24),
                                    env_int("MRT_TRACE_LEAFMIN", 8), wide };
     return t;
 }
@@ -236,7 +236,7 @@ void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const voi
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
     const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin));
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); uint32_t need = (warpsNeeded + 3u) / 4u; return need < cap ? need : cap; };
-#define MRT_LAUNCH_ISECT(MB, WD) k_intersect_persistent<MB, WD><<<blocks(MB), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin)
+#define MRT_LAUNCH_ISECT(MB, WD) k_intersect_persistent<MB, WD><<<blocks(MB), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin, 0x47000000u)
     if (t.wide) {
         if (t.minb >= 12) MRT_LAUNCH_ISECT(12, 1); else if (t.minb >= 10) MRT_LAUNCH_ISECT(10, 1);
         else if (t.minb >= 8) MRT_LAUNCH_ISECT(8, 1); else if (t.minb >= 6) MRT_LAUNCH_ISECT(6, 1); else MRT_LAUNCH_ISECT(5, 1);
@@ -254,7 +254,7 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     const uint32_t parity = wave & 1u;
     const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
-#define MRT_LAUNCH_TRACE(MB, WD) k_wf_trace<MB, WD><<<blocks(MB), 128, 0, s>>>(p.S, b, parity, refill, leafMin, p.counters)
+#define MRT_LAUNCH_TRACE(MB, WD) k_wf_trace<MB, WD><<<blocks(MB), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters)
     if (t.wide) {
         if (t.minb >= 12) MRT_LAUNCH_TRACE(12, 1); else if (t.minb >= 10) MRT_LAUNCH_TRACE(10, 1);
         else if (t.minb >= 8) MRT_LAUNCH_TRACE(8, 1); else if (t.minb >= 6) MRT_LAUNCH_TRACE(6, 1); else MRT_LAUNCH_TRACE(5, 1);
