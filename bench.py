@@ -196,9 +196,11 @@ def run_ours(args, wl):
     for s in range(3):
         r.update_noise(s, init)
 
-    span = (F - 1) * world + 1                        # tiles for frames first .. first+(F-1)*world
-    host_tiles = torch.empty((span, m.NOISE_TILE_FLOATS), dtype=torch.float32, pin_memory=True)
-    m.noise_tiles(wl["seed"], 0, span, out=host_tiles.numpy())
+    from mrt_b200.distributed import lead_in_frames, plan_sample_shard
+    n_tiles = F * world                               # tile j belongs to frame (step start + j); reused every step
+    span = (F - 1) * world + 1                        # tiles one rank consumes: frames first .. first+(F-1)*world
+    host_tiles = torch.empty((n_tiles, m.NOISE_TILE_FLOATS), dtype=torch.float32, pin_memory=True)
+    m.noise_tiles(wl["seed"], 0, n_tiles, out=host_tiles.numpy())
     dev_tiles = host_tiles.to(f"cuda:{dev}")
     host_image = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
     img_ptr, img_bytes = r.image_device_ptr()
@@ -210,11 +212,16 @@ def run_ours(args, wl):
 
     state = {"frame": 0}
 
+    tile_bytes = m.NOISE_TILE_FLOATS * 4
+
     def step(tiles_ptr, readback):
-        first = state["frame"] + rank
+        plan = plan_sample_shard(state["frame"], F, rank, world)
+        first = plan.first_frame
         if world > 1:
+            for f in lead_in_frames(first):           # slots of the two frames before this rank's first one
+                r.update_noise_from(f % 3, tiles_ptr + ((f - state["frame"]) % n_tiles) * tile_bytes)
             r.clear_image()
-        r.draw(F, tiles_ptr, first_frame=first, frame_stride=world, sync=False)
+        r.draw(F, tiles_ptr + rank * tile_bytes, first_frame=first, frame_stride=world, sync=False)
         if world > 1:
             r.sync()
             dist.all_reduce(image_t)                  # one NCCL sum of the W*H*float4 image per step
@@ -248,6 +255,7 @@ def run_ours(args, wl):
         step(dev_tiles.data_ptr(), False)
     barrier()
     r.reset_stats()
+    r.set_profile(True)      # CUDA-event pair around every trace-kernel launch (the dominant kernel) on the ctx stream
 
     # ---- timed: inputs resident in HBM, CUDA events on the launching stream --------------------------------------
     with ClockSampler(dev) as clocks:
@@ -269,6 +277,8 @@ def run_ours(args, wl):
     value = rays / (ms * 1e-3) / 1e6
     launches = st["kernel_launches"]
     kernel_ms = st["last_kernel_ms"]
+    trace_ms, trace_launches = st["profile_trace_ms"], st["profile_trace_launches"]      # last step of the timed region
+    r.set_profile(False)
 
     # ---- e2e: host buffers, H2D of the noise tiles and D2H of the image inside every step ------------------------
     barrier()
@@ -284,9 +294,14 @@ def run_ours(args, wl):
 
     if rank == 0:
         peak, peak_kind = measured_peaks()
-        alg_bytes = (BYTES_PER_SAMPLE * W * H * F + BYTES_PER_SEGMENT * st["primary_rays"] / args.steps)   # per launch, this rank
-        per_launch_ms = dev_ms / args.steps
-        achieved = alg_bytes / (per_launch_ms * 1e-3) / 1e9
+        # dominant kernel = k_wf_trace: per ray it reads 32 B of ray and writes a 16-B Intersection (48 B for the
+        # primary and 48 B for the light-sampling intersect); per launch = 48 B x rays traced in that launch
+        rays_per_step = rays_local / args.steps
+        alg_bytes_step = BYTES_PER_SAMPLE * W * H * F + BYTES_PER_SEGMENT * st["primary_rays"] / args.steps
+        trace_launches = max(trace_launches, 1)
+        alg_bytes = BYTES_PER_RAY_TRACE * rays_per_step / trace_launches
+        per_launch_ms = trace_ms / trace_launches
+        achieved = alg_bytes / max(per_launch_ms * 1e-3, 1e-12) / 1e9
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -294,16 +309,23 @@ def run_ours(args, wl):
             "msamples_per_s": samples / (ms * 1e-3) / 1e6,
             "rays_per_sample": rays / samples,
             "wall_ms_per_step": wall_ms / args.steps,
-            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(host_tiles.numel() * 4),
+            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int((span + (2 if world > 1 else 0)) * tile_bytes),
                     "d2h_bytes_per_step": int(host_image.numel() * 4), "msamples_per_s": samples / e2e_s / 1e6,
                     "image_finite": finite},
             "gpu_launches": int(launches),
             "clocks": clocks.summary(),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                         "peak_kind": peak_kind, "kernel": "k_render_fused", "algorithmic_bytes_per_launch": alg_bytes,
-                         "launch_ms": per_launch_ms, "last_kernel_ms": kernel_ms,
-                         "note": "algorithmic bytes = 140 B/sample + 376 B/live segment of the reference's stage buffers (SURVEY §8d); "
-                                 "the fused kernel keeps them in registers, so this path is latency/issue-bound, not HBM-bound"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": NCU_TRACE_DRAM_BYTES_PER_LAUNCH,
+                         "peak_kind": peak_kind, "kernel": "k_wf_trace", "algorithmic_bytes_per_launch": alg_bytes,
+                         "launch_ms": per_launch_ms, "launches_per_step": trace_launches,
+                         "kernel_share_of_step": trace_ms / max(dev_ms / args.steps, 1e-9),
+                         "step_algorithmic_bytes": alg_bytes_step,
+                         "step_achieved_gbs": alg_bytes_step / (dev_ms / args.steps * 1e-3) / 1e9,
+                         "issue_slot_utilisation_ncu": NCU_TRACE_ISSUE_ACTIVE,
+                         "note": "BVH traversal is not a streaming kernel: ncu shows it bound by instruction issue on the ALU pipe "
+                                 "(issue slots 71 % busy, ALU pipe 69 %, DRAM < 5 %), so the HBM fraction is small by construction; "
+                                 "traffic = dram bytes of one full-size launch from profiles/ (ncu --set full); algorithmic bytes = "
+                                 "48 B per ray traced (32 B ray + 16 B Intersection, SURVEY 8d)"},
             "bvh": {"nodes": st["bvh_nodes"], "depth": st["bvh_depth"], "sah_cost": st["bvh_sah_cost"], "build_ms": st["bvh_build_ms"]},
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -93,7 +93,8 @@ typedef struct mrt_stats {
     float    last_kernel_ms;    /* device time of the kernels alone inside the last mrt_render_frames */
     uint32_t bvh8_nodes;        /* 8-wide quantised tree the production trace kernel traverses (80-byte nodes) */
     uint32_t bvh8_depth;
-    uint32_t reserved[2];
+    float    profile_trace_ms;  /* mrt_set_profile(1): summed CUDA-event time of the k_wf_trace launches of the last mrt_render_frames */
+    uint32_t profile_trace_launches;   /* ... and how many of them found work (queue not empty) */
 } mrt_stats;
 
 /* Read-only view of a host scene container (arrays in the ABI layouts of mrt_abi.h). */
@@ -142,6 +143,9 @@ int mrt_set_noise(mrt_ctx* ctx, uint32_t slot, const float* tile);
 int mrt_set_row_shard(mrt_ctx* ctx, uint32_t first_row, uint32_t row_stride);
 int mrt_set_accumulate_mode(mrt_ctx* ctx, uint32_t mode);
 int mrt_set_pipeline(mrt_ctx* ctx, uint32_t pipeline);
+/* 1: bracket every trace-kernel launch of mrt_render_frames (wavefront pipeline) with a CUDA event pair on the ctx stream,
+ * so that mrt_get_stats can report the dominant kernel's own device time (costs two event records per wave). */
+int mrt_set_profile(mrt_ctx* ctx, uint32_t on);
 
 /* ---- the six dispatch kinds, one entry point each (asynchronous on the ctx stream) ---------- */
 /* rayGenerator, Shaders.metal:75-103; bindings Renderer.mm:508-510 (noise slot frame%3). */

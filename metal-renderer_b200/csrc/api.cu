@@ -59,6 +59,9 @@ struct mrt_ctx {
     void* dTriSlot = nullptr;                    // original triangle index -> leaf-order record
     void* dNodes8 = nullptr; void* dTris8 = nullptr;   // 8-wide tree (bvh8.h)
     WfBuffers wf{};                              // wavefront path state + queues (sized by mrt_resize)
+    bool profile = false;                        // event pair around every trace launch
+    std::vector<cudaEvent_t> profEvents; size_t profUsed = 0;
+    unsigned int* dWaveCounts = nullptr; size_t waveCountCap = 0;   // per-wave queue sizes (profile mode)
     void* wfArena = nullptr;
     mrt_stats stats{};
 
@@ -161,7 +164,8 @@ int mrt_destroy(mrt_ctx* c) {
     cudaSetDevice(c->cfg.device);
     cudaStreamSynchronize(c->stream);
     free_scene(c); free_sized(c);
-    cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters); cudaFree(c->dHead);
+    cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters); cudaFree(c->dHead); cudaFree(c->dWaveCounts);
+    for (auto& e : c->profEvents) cudaEventDestroy(e);
     if (c->hFrameTable) cudaFreeHost(c->hFrameTable);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->evK0); cudaEventDestroy(c->evK1); cudaEventDestroy(c->tableCopied);
     for (auto& e : c->user) cudaEventDestroy(e);
@@ -294,7 +298,7 @@ int mrt_set_noise(mrt_ctx* c, uint32_t slot, const float* tile) {
     NEED(c && tile, MRT_E_INVALID, "NULL argument");
     NEED(slot < MRT_NOISE_SLOTS, MRT_E_INVALID, "slot %u out of range", slot);
     CK(cudaSetDevice(c->cfg.device));
-    CK(cudaMemcpyAsync(c->dNoisePool + slot * kTileFloat4, tile, kTileBytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->dNoisePool + slot * kTileFloat4, tile, kTileBytes, cudaMemcpyDefault, c->stream));   // host or device tile
     return MRT_OK;
 }
 
@@ -307,6 +311,11 @@ int mrt_set_row_shard(mrt_ctx* c, uint32_t first_row, uint32_t row_stride) {
 int mrt_set_accumulate_mode(mrt_ctx* c, uint32_t mode) {
     NEED(c && mode <= MRT_ACCUM_REPLACE, MRT_E_INVALID, "bad accumulate mode");
     c->cfg.accumulate_mode = mode;
+    return MRT_OK;
+}
+int mrt_set_profile(mrt_ctx* c, uint32_t on) {
+    NEED(c, MRT_E_INVALID, "ctx is NULL");
+    c->profile = on != 0;
     return MRT_OK;
 }
 int mrt_set_pipeline(mrt_ctx* c, uint32_t pipeline) {
@@ -433,10 +442,26 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             const bool count = c->cfg.count_rays != 0;
             launch_wf_shade(c->stream, p, b, 0, true, count);
             const uint64_t waves = (uint64_t)n_frames * c->cfg.max_path_length;
+            c->profUsed = 0;
+            if (c->profile) {
+                while (c->profEvents.size() < 2 * waves) { cudaEvent_t e; CK(cudaEventCreate(&e)); c->profEvents.push_back(e); }
+                if (c->waveCountCap < waves) {
+                    cudaFree(c->dWaveCounts); c->dWaveCounts = nullptr; c->waveCountCap = 0;
+                    CK(cudaMalloc(&c->dWaveCounts, waves * 2 * sizeof(unsigned int)));
+                    c->waveCountCap = waves;
+                }
+            }
             for (uint64_t w = 0; w < waves; ++w) {
+                if (c->profile) {
+                    // queue sizes of this wave (the trace kernel clears the other pair, so copy them out first)
+                    CK(cudaMemcpyAsync(c->dWaveCounts + 2 * w, b.counts + 2 * (w & 1u), 2 * sizeof(unsigned int), cudaMemcpyDeviceToDevice, c->stream));
+                    CK(cudaEventRecord(c->profEvents[2 * w], c->stream));
+                }
                 launch_wf_trace(c->stream, p, b, (uint32_t)(w & 1u));
+                if (c->profile) CK(cudaEventRecord(c->profEvents[2 * w + 1], c->stream));
                 launch_wf_shade(c->stream, p, b, (uint32_t)(w & 1u), false, count);
             }
+            if (c->profile) c->profUsed = 2 * waves;
             LAUNCHED(c, 1 + 2 * waves);
         }
         CK(cudaEventRecord(c->evK1, c->stream));
@@ -539,6 +564,17 @@ int mrt_get_stats(mrt_ctx* c, mrt_stats* out) {
     c->stats.primary_rays = h[0]; c->stats.shadow_rays = h[1]; c->stats.nodes_visited = h[2]; c->stats.triangles_tested = h[3];
     if (c->timed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->ev0, c->ev1)); c->stats.last_render_ms = ms; }
     if (c->kernelTimed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->evK0, c->evK1)); c->stats.last_kernel_ms = ms; }
+    if (c->profUsed) {
+        std::vector<unsigned int> wc(c->profUsed);
+        CK(cudaMemcpy(wc.data(), c->dWaveCounts, c->profUsed * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+        double sum = 0.0; uint32_t n = 0;
+        for (size_t w = 0; w < c->profUsed / 2; ++w) {
+            if (wc[2 * w] + wc[2 * w + 1] == 0) continue;                 // empty wave: the kernel returned at once
+            float ms = 0; CK(cudaEventElapsedTime(&ms, c->profEvents[2 * w], c->profEvents[2 * w + 1]));
+            sum += ms; ++n;
+        }
+        c->stats.profile_trace_ms = (float)sum; c->stats.profile_trace_launches = n;
+    }
     *out = c->stats;
     return MRT_OK;
 }

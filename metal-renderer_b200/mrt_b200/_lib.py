@@ -49,7 +49,8 @@ class Stats(C.Structure):
                 ("frames_rendered", C.c_uint64), ("nodes_visited", C.c_uint64), ("triangles_tested", C.c_uint64),
                 ("last_render_ms", C.c_float), ("bvh_nodes", C.c_uint32), ("bvh_depth", C.c_uint32),
                 ("bvh_sah_cost", C.c_float), ("bvh_build_ms", C.c_float), ("last_kernel_ms", C.c_float),
-                ("bvh8_nodes", C.c_uint32), ("bvh8_depth", C.c_uint32), ("reserved", C.c_uint32 * 2)]
+                ("bvh8_nodes", C.c_uint32), ("bvh8_depth", C.c_uint32), ("profile_trace_ms", C.c_float),
+                ("profile_trace_launches", C.c_uint32)]
 
 
 class SceneView(C.Structure):
@@ -87,6 +88,7 @@ SIGNATURES = {
     "mrt_set_row_shard": (C.c_int, [_P, _U32, _U32]),
     "mrt_set_accumulate_mode": (C.c_int, [_P, _U32]),
     "mrt_set_pipeline": (C.c_int, [_P, _U32]),
+    "mrt_set_profile": (C.c_int, [_P, _U32]),
     "mrt_raygen": (C.c_int, [_P, _U32]),
     "mrt_intersect": (C.c_int, [_P, _U32]),
     "mrt_shade": (C.c_int, [_P, _U32, _U32]),

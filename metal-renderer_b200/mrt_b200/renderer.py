@@ -68,11 +68,18 @@ class Renderer:
         L.check(L.lib().mrt_set_noise(self._ctx, slot, L.ptr(tile)))
         L.check(L.lib().mrt_sync(self._ctx))          # tile is borrowed only for this call
 
+    def update_noise_from(self, slot, address):
+        """Same, from a raw host or device address (asynchronous: the memory must stay valid until sync())."""
+        L.check(L.lib().mrt_set_noise(self._ctx, slot, C.c_void_p(int(address))))
+
     def set_row_shard(self, first_row, row_stride):
         L.check(L.lib().mrt_set_row_shard(self._ctx, first_row, row_stride))
 
     def set_accumulate_mode(self, mode):
         L.check(L.lib().mrt_set_accumulate_mode(self._ctx, mode))
+
+    def set_profile(self, on):
+        L.check(L.lib().mrt_set_profile(self._ctx, int(on)))
 
     def set_pipeline(self, pipeline):
         L.check(L.lib().mrt_set_pipeline(self._ctx, pipeline))
