@@ -41,6 +41,10 @@ WORKLOADS = {   # BASELINE.json configs; SURVEY.md §8(d) "Concrete inputs"
 DEFAULT_WORKLOAD = "spheres-1m-1080p"
 BYTES_PER_SEGMENT = 376      # 48 intersect + 224 shade + 48 shadow intersect + 56 resolve
 BYTES_PER_SAMPLE = 140       # raygen 16+80, accumulate 12+16+16
+BYTES_PER_RAY_TRACE = 48     # one intersect: 32 B of ray read + 16 B Intersection written
+# from profiles/r1_f_wf_trace_ncu_summary.txt (ncu --set full of one full-size k_wf_trace launch, 1M triangles, 1080p)
+NCU_TRACE_DRAM_BYTES_PER_LAUNCH = 274_450_176       # 242.99 MB read + 31.46 MB written
+NCU_TRACE_ISSUE_ACTIVE = 0.713
 
 
 def measured_peaks():
