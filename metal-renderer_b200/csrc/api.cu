@@ -62,6 +62,7 @@ struct mrt_ctx {
     bool profile = false;                        // event pair around every trace launch
     std::vector<cudaEvent_t> profEvents; size_t profUsed = 0;
     unsigned int* dWaveCounts = nullptr; size_t waveCountCap = 0;   // per-wave queue sizes (profile mode)
+    float4* dSamples = nullptr; size_t sampleCap = 0;            // per-sample radiance of a wavefront batch
     void* wfArena = nullptr;
     mrt_stats stats{};
 
@@ -164,7 +165,7 @@ int mrt_destroy(mrt_ctx* c) {
     cudaSetDevice(c->cfg.device);
     cudaStreamSynchronize(c->stream);
     free_scene(c); free_sized(c);
-    cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters); cudaFree(c->dHead); cudaFree(c->dWaveCounts);
+    cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters); cudaFree(c->dHead); cudaFree(c->dWaveCounts); cudaFree(c->dSamples);
     for (auto& e : c->profEvents) cudaEventDestroy(e);
     if (c->hFrameTable) cudaFreeHost(c->hFrameTable);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->evK0); cudaEventDestroy(c->evK1); cudaEventDestroy(c->tableCopied);
@@ -286,10 +287,10 @@ int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
         auto takeU = [&]() { uint32_t* r = reinterpret_cast<uint32_t*>(p); p += u4; return r; };
         c->wf.P0 = take4(); c->wf.P1 = take4(); c->wf.P2 = take4(); c->wf.P3 = take4(); c->wf.H = take4();
         c->wf.S0 = take4(); c->wf.S1 = take4();
-        c->wf.visible = takeU(); c->wf.cursor = takeU();
+        c->wf.visible = takeU(); c->wf.item = takeU();
         c->wf.queueExt[0] = takeU(); c->wf.queueExt[1] = takeU(); c->wf.queueShadow[0] = takeU(); c->wf.queueShadow[1] = takeU();
-        c->wf.counts = reinterpret_cast<unsigned int*>(p); c->wf.heads = c->wf.counts + 4;
-        c->wf.slots = (uint32_t)slots;
+        c->wf.counts = reinterpret_cast<unsigned int*>(p); c->wf.heads = c->wf.counts + 4; c->wf.workHead = c->wf.counts + 6;
+        c->wf.slots = (uint32_t)slots; c->wf.pixels = (uint32_t)slots;
     }
     return MRT_OK;
 }
@@ -434,35 +435,64 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             launch_render_fused(c->stream, p, c->cfg.count_rays != 0);
             LAUNCHED(c, 1);
         } else {
-            // queue-compacted wavefront: init wave, then at most n_frames * L {trace, shade} waves (a slot needs one
-            // trace per path segment); waves that find both queues empty return at once
+            // queue-compacted wavefront.  Work items (frame, pixel) are handed to path slots dynamically; finished samples
+            // go to a per-sample buffer and are folded into the image in frame order at the end.  The batch is cut into
+            // sub-batches so that the sample buffer (16 B per sample) stays within a quarter of the free device memory.
             WfBuffers b = c->wf;
-            b.slots = ((c->W + 7u) / 8u) * ((p.ownedRows + 3u) / 4u) * 32u;
-            CK(cudaMemsetAsync(b.counts, 0, 6 * sizeof(unsigned int), c->stream));
+            b.pixels = ((c->W + 7u) / 8u) * ((p.ownedRows + 3u) / 4u) * 32u;
+            b.slots = b.pixels;
             const bool count = c->cfg.count_rays != 0;
-            launch_wf_shade(c->stream, p, b, 0, true, count);
-            const uint64_t waves = (uint64_t)n_frames * c->cfg.max_path_length;
+            size_t freeB = 0, totalB = 0;
+            CK(cudaMemGetInfo(&freeB, &totalB));
+            const size_t perFrame = (size_t)std::max(1u, b.pixels) * sizeof(float4);
+            const size_t budget = std::max(perFrame, std::min<size_t>((freeB + c->sampleCap) / 4, (size_t)24 << 30));
+            const uint32_t maxSub = (uint32_t)std::max<size_t>(1, std::min<size_t>(budget / perFrame, n_frames));
+            if (c->sampleCap < (size_t)maxSub * perFrame) {
+                CK(cudaStreamSynchronize(c->stream));
+                cudaFree(c->dSamples); c->dSamples = nullptr; c->sampleCap = 0;
+                CK(cudaMalloc(&c->dSamples, (size_t)maxSub * perFrame));
+                c->sampleCap = (size_t)maxSub * perFrame;
+            }
+            b.samples = c->dSamples;
             c->profUsed = 0;
+            // waves per sub-batch of nf frames: greedy assignment finishes within (total segments / slots) + L waves, plus
+            // one wave per padding pixel a slot may draw; waves that find both queues empty return at once
+            const uint32_t Lp = c->cfg.max_path_length;
+            auto waves_for = [Lp](uint32_t nf) { return (uint64_t)nf * Lp + Lp + 2; };
+            uint64_t wavesTotal = 0;
+            for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) wavesTotal += waves_for(std::min(maxSub, n_frames - f0));
             if (c->profile) {
-                while (c->profEvents.size() < 2 * waves) { cudaEvent_t e; CK(cudaEventCreate(&e)); c->profEvents.push_back(e); }
-                if (c->waveCountCap < waves) {
+                while (c->profEvents.size() < 2 * wavesTotal) { cudaEvent_t e; CK(cudaEventCreate(&e)); c->profEvents.push_back(e); }
+                if (c->waveCountCap < wavesTotal) {
                     cudaFree(c->dWaveCounts); c->dWaveCounts = nullptr; c->waveCountCap = 0;
-                    CK(cudaMalloc(&c->dWaveCounts, waves * 2 * sizeof(unsigned int)));
-                    c->waveCountCap = waves;
+                    CK(cudaMalloc(&c->dWaveCounts, wavesTotal * 2 * sizeof(unsigned int)));
+                    c->waveCountCap = wavesTotal;
                 }
             }
-            for (uint64_t w = 0; w < waves; ++w) {
-                if (c->profile) {
-                    // queue sizes of this wave (the trace kernel clears the other pair, so copy them out first)
-                    CK(cudaMemcpyAsync(c->dWaveCounts + 2 * w, b.counts + 2 * (w & 1u), 2 * sizeof(unsigned int), cudaMemcpyDeviceToDevice, c->stream));
-                    CK(cudaEventRecord(c->profEvents[2 * w], c->stream));
+            uint64_t launched = 0, pw = 0;
+            for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) {
+                const uint32_t nf = std::min(maxSub, n_frames - f0);
+                RenderParams q = p;
+                q.frames = c->dFrameTable + f0; q.nFrames = nf;
+                b.totalItems = (unsigned long long)nf * b.pixels;
+                CK(cudaMemsetAsync(b.counts, 0, 7 * sizeof(unsigned int), c->stream));     // counts[4], heads[2], workHead
+                launch_wf_shade(c->stream, q, b, 0, true, count);
+                const uint64_t waves = waves_for(nf);
+                for (uint64_t w = 0; w < waves; ++w, ++pw) {
+                    if (c->profile) {
+                        // queue sizes of this wave (the trace kernel clears the other pair, so copy them out first)
+                        CK(cudaMemcpyAsync(c->dWaveCounts + 2 * pw, b.counts + 2 * (w & 1u), 2 * sizeof(unsigned int), cudaMemcpyDeviceToDevice, c->stream));
+                        CK(cudaEventRecord(c->profEvents[2 * pw], c->stream));
+                    }
+                    launch_wf_trace(c->stream, q, b, (uint32_t)(w & 1u));
+                    if (c->profile) CK(cudaEventRecord(c->profEvents[2 * pw + 1], c->stream));
+                    launch_wf_shade(c->stream, q, b, (uint32_t)(w & 1u), false, count);
                 }
-                launch_wf_trace(c->stream, p, b, (uint32_t)(w & 1u));
-                if (c->profile) CK(cudaEventRecord(c->profEvents[2 * w + 1], c->stream));
-                launch_wf_shade(c->stream, p, b, (uint32_t)(w & 1u), false, count);
+                launch_wf_resolve_samples(c->stream, q, b);
+                launched += 2 + 2 * waves;
             }
-            if (c->profile) c->profUsed = 2 * waves;
-            LAUNCHED(c, 1 + 2 * waves);
+            if (c->profile) c->profUsed = 2 * pw;
+            LAUNCHED(c, launched);
         }
         CK(cudaEventRecord(c->evK1, c->stream));
         c->kernelTimed = true;
@@ -561,6 +591,11 @@ int mrt_get_stats(mrt_ctx* c, mrt_stats* out) {
     CK(cudaStreamSynchronize(c->stream));
     unsigned long long h[4];
     CK(cudaMemcpy(h, c->dCounters, sizeof h, cudaMemcpyDeviceToHost));
+    if (c->wf.counts) {
+        unsigned int undrained = 0;
+        CK(cudaMemcpy(&undrained, c->wf.counts + 7, sizeof undrained, cudaMemcpyDeviceToHost));
+        NEED(undrained == 0, MRT_E_STATE, "wavefront batch ended with %u rays still queued (wave bound too small)", undrained);
+    }
     c->stats.primary_rays = h[0]; c->stats.shadow_rays = h[1]; c->stats.nodes_visited = h[2]; c->stats.triangles_tested = h[3];
     if (c->timed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->ev0, c->ev1)); c->stats.last_render_ms = ms; }
     if (c->kernelTimed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->evK0, c->evK1)); c->stats.last_kernel_ms = ms; }

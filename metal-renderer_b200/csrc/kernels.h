@@ -54,18 +54,24 @@ struct WfBuffers {
     float4* H;           // nearest hit of the extension ray: t, triangle, u, v   (Intersection, Raytracing.h:85-90)
     float4* S0;          // light-sampling ray: direction.xyz, distance of the target along it
     float4* S1;          //                     throughput.xyz, targetIndex      (LightSamplingRay, Raytracing.h:71-83)
-    uint32_t* visible;   // 1 iff the light-sampling ray's nearest hit is its target (Shaders.metal:225)
-    uint32_t* cursor;    // bits 0..30: index into the frame table of the sample in flight; bit 31: light ray pending
+    uint32_t* visible;   // written by trace: 1 iff the light-sampling ray's nearest hit is its target (Shaders.metal:225),
+                         // 0 if not; written by shade: 2 = light ray queued, 3 = none
+    uint32_t* item;      // work item (frame-table entry * pixels + pixel) the slot is tracing; 0xFFFFFFFF none, ..FE retry
+    float4* samples;     // radiance of every finished sample of the batch: [frame-table entry][pixel]
+    unsigned int* workHead;  // next unclaimed work item
+    unsigned long long totalItems;   // nFrames * pixels
+    uint32_t pixels;     // owned pixels in 8x4-tiled order, padded: tilesX * tilesY * 32
     uint32_t* queueExt[2];
     uint32_t* queueShadow[2];
     unsigned int* counts;    // [parity][0 ext, 1 shadow]
     unsigned int* heads;     // [parity] work counter of the persistent trace kernel
     const uint32_t* triSlot; // original triangle index -> record in triRecords
     const float4* triRecords;// the triangle records the trace kernel uses (wide or binary tree order)
-    uint32_t slots;          // tilesX * tilesY * 32
+    uint32_t slots;          // path slots in flight (<= pixels)
 };
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays);
 void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave);
+void launch_wf_resolve_samples(cudaStream_t s, const RenderParams& p, const WfBuffers& b);
 bool trace_uses_wide_bvh();   // MRT_BVH_WIDTH=2 selects the binary tree (A/B runs); default 8
 int wf_kernel_info(int* traceRegs, int* traceBlocksPerSM, int* shadeRegs);
 

@@ -104,91 +104,126 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     else trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
 }
 
-// ---- k_wf_shade: resolve -> intersectionHandler -> accumulate/regenerate, queue compaction ----------------------
-// slot -> pixel: 32 consecutive slots are one 8x4 pixel tile (primary rays of a warp stay coherent).
+// ---- k_wf_shade: resolve -> intersectionHandler -> sample done? -> next work item, queue compaction ---------------
+// Work item w = k * pixels + pix: sample of frame-table entry k at owned pixel pix (32 consecutive pix = one 8x4 tile,
+// so primary rays of neighbouring items stay coherent).  A slot that finishes its sample writes the radiance to the
+// per-sample buffer and takes the NEXT unclaimed item, whatever pixel it belongs to: slots never idle while work is
+// left (with one slot tied to one pixel, pixels whose paths always run to the length limit kept a thin tail of waves
+// alive for L * frames waves — pass G: 1024 launches averaging 77 % of a full wave).  k_wf_resolve_samples then folds
+// the samples into the image in frame order, which is what keeps the running mean of Shaders.metal:241-247 bit-exact.
+#define MRT_ITEM_NONE  0xFFFFFFFFu      /* slot has nothing to do (and will not get anything: work exhausted) */
+#define MRT_ITEM_RETRY 0xFFFFFFFEu      /* slot drew a padding pixel: fetch again next wave */
+
+__device__ __forceinline__ bool wf_pixel_of(uint32_t pix, const RenderParams& P, uint32_t& x, uint32_t& y) {
+    const uint32_t tilesX = (P.g.W + 7u) >> 3;
+    const uint32_t tile = pix >> 5, l = pix & 31u;
+    x = (tile % tilesX) * 8u + (l & 7u);
+    const uint32_t row = (tile / tilesX) * 4u + (l >> 3);
+    y = P.g.rowFirst + row * P.g.rowStride;
+    return x < P.g.W && row < P.ownedRows;
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, uint32_t outParity, uint32_t first) {
-    __shared__ uint32_t sE[8], sS[8], sN[8], sBase[2];
+    __shared__ uint32_t sE[8], sS[8], sN[8], sW[8], sBase[3];
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t tilesX = (P.g.W + 7u) >> 3;
-    const uint32_t tile = slot >> 5;
-    const uint32_t x = (tile % tilesX) * 8u + (lane & 7u);
-    const uint32_t row = (tile / tilesX) * 4u + (lane >> 3);
-    const uint32_t y = P.g.rowFirst + row * P.g.rowStride;
-    const bool valid = slot < b.slots && x < P.g.W && row < P.ownedRows;
+    const unsigned lt = (1u << lane) - 1u;
+    const bool valid = slot < b.slots;
     const size_t tileStride = MRT_NOISE_DIMENSIONS * MRT_NOISE_DIMENSIONS;
-    bool pushE = false, pushS = false;
+    bool pushE = false, pushS = false, need = false;
     uint32_t liveShadow = 0;
+    uint32_t item = MRT_ITEM_NONE;
+    PathState st;
+    st.origin = st.direction = st.throughput = st.radiance = mk3(0.f, 0.f, 0.f); st.pdf = st.prevDiffuse = st.bounce = st.ior = 0.f;
 
     if (valid) {
-        const uint32_t cw = first ? 0u : b.cursor[slot];
-        uint32_t k = cw & 0x7fffffffu;
-        if (k < P.nFrames) {
-            PathState st;
-            bool gen = first != 0;
-            uint32_t pending = 0;
-            if (!first) {
-                float4 p0 = b.P0[slot], p1 = b.P1[slot], p2 = b.P2[slot], p3 = b.P3[slot];
-                st.origin = mk3(p0.x, p0.y, p0.z); st.pdf = p0.w;
-                st.direction = mk3(p1.x, p1.y, p1.z); st.prevDiffuse = p1.w;
-                st.throughput = mk3(p2.x, p2.y, p2.z); st.bounce = p2.w;
-                st.radiance = mk3(p3.x, p3.y, p3.z); st.ior = p3.w;
-                const uint4 e = __ldg(P.frames + k);
-                if (cw >> 31) {                                                        // Shaders.metal:225-229
-                    if (b.visible[slot]) { float4 s1 = b.S1[slot]; st.radiance = st.radiance + mk3(s1.x, s1.y, s1.z); }
-                }
-                const float4 h = b.H[slot];
-                bool finished;
-                if (h.x < MRT_DISTANCE_EPSILON) {                                      // Shaders.metal:122-126
-                    finished = true;
-                } else {
-                    HitRec hit; hit.t = h.x; hit.tri = __float_as_uint(h.y); hit.u = h.z; hit.v = h.w;
-                    const uint32_t s = (e.x + uint32_t(st.bounce)) % 3u;               // Renderer.mm:538
-                    const uint32_t t = s == 0 ? e.y : (s == 1 ? e.z : e.w);
-                    ShadowRay sh; bool nee;
-                    const bool live = intersection_handler(P.S, hit, st, sh, nee, P.noisePool + t * tileStride, e.x,
-                                                           P.maxPathLength, x, y);
-                    if (live) {
-                        liveShadow = 1;
-                        // the light-sampling ray can only count if it reaches its target at t >= DISTANCE_EPSILON
-                        HitRec tg; tg.t = INFINITY; tg.tri = MRT_NO_HIT; tg.u = tg.v = 0.0f;
-                        triangle_test(b.triRecords, __ldg(b.triSlot + sh.targetIndex), st.origin, sh.direction, 0.0f, INFINITY, tg);
-                        if (tg.tri == sh.targetIndex && tg.t >= MRT_DISTANCE_EPSILON) {
-                            pushS = true; pending = 1;
-                            b.S0[slot] = make_float4(sh.direction.x, sh.direction.y, sh.direction.z, tg.t);
-                            b.S1[slot] = make_float4(sh.throughput.x, sh.throughput.y, sh.throughput.z, __uint_as_float(sh.targetIndex));
-                        }
-                    }
-                    finished = uint32_t(st.bounce) >= P.maxPathLength;
-                }
-                if (finished) {                                                        // Shaders.metal:239-248
-                    const uint32_t pix = y * P.g.W + x;
-                    const float4 c = P.image[pix];
-                    const f3 color = accumulate_image(st.radiance, mk3(c.x, c.y, c.z), e.x, P.accumMode);
-                    P.image[pix] = make_float4(color.x, color.y, color.z, 1.0f);
-                    ++k; gen = true; pending = 0; pushS = false;
-                }
+        item = first ? MRT_ITEM_RETRY : b.item[slot];
+        if (item == MRT_ITEM_RETRY) need = true;
+        else if (item != MRT_ITEM_NONE) {
+            const uint32_t k = item / b.pixels, pix = item - k * b.pixels;
+            uint32_t x, y;
+            wf_pixel_of(pix, P, x, y);
+            float4 p0 = b.P0[slot], p1 = b.P1[slot], p2 = b.P2[slot], p3 = b.P3[slot];
+            st.origin = mk3(p0.x, p0.y, p0.z); st.pdf = p0.w;
+            st.direction = mk3(p1.x, p1.y, p1.z); st.prevDiffuse = p1.w;
+            st.throughput = mk3(p2.x, p2.y, p2.z); st.bounce = p2.w;
+            st.radiance = mk3(p3.x, p3.y, p3.z); st.ior = p3.w;
+            const uint4 e = __ldg(P.frames + k);
+            if (b.visible[slot] == 1u) {                                               // Shaders.metal:225-229
+                float4 s1 = b.S1[slot]; st.radiance = st.radiance + mk3(s1.x, s1.y, s1.z);
             }
-            if (gen) {
-                if (k < P.nFrames) {
-                    const uint4 e = __ldg(P.frames + k);
-                    const uint32_t s = e.x % 3u;
-                    const uint32_t t = s == 0 ? e.y : (s == 1 ? e.z : e.w);
-                    ray_generator(st, P.noisePool + t * tileStride, x, y, P.g.W, P.g.H);   // Renderer.mm:508-512
-                    pushE = true;
+            const float4 h = b.H[slot];
+            bool finished;
+            if (h.x < MRT_DISTANCE_EPSILON) {                                          // Shaders.metal:122-126
+                finished = true;
+            } else {
+                HitRec hit; hit.t = h.x; hit.tri = __float_as_uint(h.y); hit.u = h.z; hit.v = h.w;
+                const uint32_t s = (e.x + uint32_t(st.bounce)) % 3u;                   // Renderer.mm:538
+                const uint32_t t = s == 0 ? e.y : (s == 1 ? e.z : e.w);
+                ShadowRay sh; bool nee;
+                const bool live = intersection_handler(P.S, hit, st, sh, nee, P.noisePool + t * tileStride, e.x,
+                                                       P.maxPathLength, x, y);
+                if (live) {
+                    liveShadow = 1;
+                    // the light-sampling ray can only count if it reaches its target at t >= DISTANCE_EPSILON
+                    HitRec tg; tg.t = INFINITY; tg.tri = MRT_NO_HIT; tg.u = tg.v = 0.0f;
+                    triangle_test(b.triRecords, __ldg(b.triSlot + sh.targetIndex), st.origin, sh.direction, 0.0f, INFINITY, tg);
+                    if (tg.tri == sh.targetIndex && tg.t >= MRT_DISTANCE_EPSILON) {
+                        pushS = true;
+                        b.S0[slot] = make_float4(sh.direction.x, sh.direction.y, sh.direction.z, tg.t);
+                        b.S1[slot] = make_float4(sh.throughput.x, sh.throughput.y, sh.throughput.z, __uint_as_float(sh.targetIndex));
+                    }
                 }
+                finished = uint32_t(st.bounce) >= P.maxPathLength;
+            }
+            if (finished) {                                // sample complete: park its radiance, ask for new work
+                b.samples[item] = make_float4(st.radiance.x, st.radiance.y, st.radiance.z, 1.0f);
+                need = true; pushS = false;
             } else {
                 pushE = true;
             }
-            if (pushE) {
-                b.P0[slot] = make_float4(st.origin.x, st.origin.y, st.origin.z, st.pdf);
-                b.P1[slot] = make_float4(st.direction.x, st.direction.y, st.direction.z, st.prevDiffuse);
-                b.P2[slot] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.bounce);
-                b.P3[slot] = make_float4(st.radiance.x, st.radiance.y, st.radiance.z, st.ior);
-            }
-            b.cursor[slot] = k | (pending << 31);
         }
+    }
+
+    // ---- claim work items: one atomic per block ----
+    const unsigned mW = __ballot_sync(0xffffffffu, need);
+    if (lane == 0) sW[warp] = __popc(mW);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t a = 0;
+        for (int w = 0; w < 8; ++w) { uint32_t n = sW[w]; sW[w] = a; a += n; }
+        sBase[2] = a ? atomicAdd(b.workHead, a) : 0u;
+    }
+    __syncthreads();
+    if (need) {
+        const unsigned long long w = (unsigned long long)sBase[2] + sW[warp] + __popc(mW & lt);
+        if (w < b.totalItems) {
+            item = (uint32_t)w;
+            const uint32_t k = item / b.pixels, pix = item - k * b.pixels;
+            uint32_t x, y;
+            if (wf_pixel_of(pix, P, x, y)) {
+                const uint4 e = __ldg(P.frames + k);
+                const uint32_t s = e.x % 3u;
+                const uint32_t t = s == 0 ? e.y : (s == 1 ? e.z : e.w);
+                ray_generator(st, P.noisePool + t * tileStride, x, y, P.g.W, P.g.H);   // Renderer.mm:508-512
+                pushE = true;
+            } else {
+                item = MRT_ITEM_RETRY;                     // padding pixel of the 8x4 tiling
+            }
+        } else {
+            item = MRT_ITEM_NONE;
+        }
+    }
+    if (valid) {
+        if (pushE) {
+            b.P0[slot] = make_float4(st.origin.x, st.origin.y, st.origin.z, st.pdf);
+            b.P1[slot] = make_float4(st.direction.x, st.direction.y, st.direction.z, st.prevDiffuse);
+            b.P2[slot] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.bounce);
+            b.P3[slot] = make_float4(st.radiance.x, st.radiance.y, st.radiance.z, st.ior);
+        }
+        b.item[slot] = item;
+        b.visible[slot] = pushS ? 2u : 3u;                 // 2 = light ray in flight (trace writes 0/1), 3 = none
     }
 
     // ---- append to the next wave's queues: warp ballots, one atomic per block and queue ----
@@ -204,9 +239,27 @@ __global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, u
         if (COUNT && aN) atomicAdd(P.counters + 1, (unsigned long long)aN);           // live light-sampling rays
     }
     __syncthreads();
-    const unsigned lt = (1u << lane) - 1u;
     if (pushE) b.queueExt[outParity][sBase[0] + sE[warp] + __popc(mE & lt)] = slot;
     if (pushS) b.queueShadow[outParity][sBase[1] + sS[warp] + __popc(mS & lt)] = slot;
+}
+
+// accumulateImage (Shaders.metal:233-249) over the batch, in frame order, one thread per owned pixel
+__global__ void __launch_bounds__(256) k_wf_resolve_samples(RenderParams P, WfBuffers b) {
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix == 0) {     // every item must have been claimed and both queue pairs drained (api.cu checks this word)
+        const unsigned int left = b.counts[0] + b.counts[1] + b.counts[2] + b.counts[3] + (*b.workHead < b.totalItems ? 1u : 0u);
+        if (left) b.counts[7] = left;
+    }
+    uint32_t x, y;
+    if (pix >= b.pixels || !wf_pixel_of(pix, P, x, y)) return;
+    const uint32_t at = y * P.g.W + x;
+    const float4 c = P.image[at];
+    f3 color = mk3(c.x, c.y, c.z);
+    for (uint32_t k = 0; k < P.nFrames; ++k) {
+        const float4 r = b.samples[(size_t)k * b.pixels + pix];
+        color = accumulate_image(mk3(r.x, r.y, r.z), color, __ldg(P.frames + k).x, P.accumMode);
+    }
+    P.image[at] = make_float4(color.x, color.y, color.z, 1.0f);
 }
 
 // ---- launchers ---------------------------------------------------------------------------------------------------
@@ -263,6 +316,11 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
         else if (t.minb >= 8) MRT_LAUNCH_TRACE(8, 0); else if (t.minb >= 6) MRT_LAUNCH_TRACE(6, 0); else MRT_LAUNCH_TRACE(5, 0);
     }
 #undef MRT_LAUNCH_TRACE
+}
+
+void launch_wf_resolve_samples(cudaStream_t s, const RenderParams& p, const WfBuffers& b) {
+    if (b.pixels == 0 || p.nFrames == 0) return;
+    k_wf_resolve_samples<<<(b.pixels + 255u) / 256u, 256, 0, s>>>(p, b);
 }
 
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays) {

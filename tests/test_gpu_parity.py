@@ -86,7 +86,7 @@ def test_config1_cornell_256_16spp_depth4_bit_exact(pipeline):
     assert_bits(gi, oi, "image")
     st, oc = r.stats(), o.counts()
     assert (st["primary_rays"], st["shadow_rays"]) == (oc["primary_rays"], oc["shadow_rays"])
-    assert st["kernel_launches"] == (1 if pipeline == m.PIPELINE_MEGAKERNEL else 1 + 2 * 16 * 4)
+    assert st["kernel_launches"] == (1 if pipeline == m.PIPELINE_MEGAKERNEL else 2 + 2 * (16 * 4 + 4 + 2))
     # primary-hit triangle IDs: bit-equal on 100% of pixels
     r2, o2 = setup_pair(scene, 256, 256)
     r2.raygen(0); o2.raygen(0); r2.intersect(); o2.intersect()
