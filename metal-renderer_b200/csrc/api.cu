@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -38,6 +39,8 @@ static const size_t kTileBytes = kTileFloat4 * sizeof(float4);
 struct mrt_ctx {
     mrt_config cfg{};
     cudaStream_t stream = nullptr;
+    cudaStream_t groupStream[4] = {nullptr, nullptr, nullptr, nullptr};      // one per wavefront slot group
+    cudaEvent_t evFork = nullptr, evJoin[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evK0 = nullptr, evK1 = nullptr, tableCopied = nullptr;
     cudaEvent_t user[8] = {};
     bool kernelTimed = false;
@@ -59,7 +62,7 @@ struct mrt_ctx {
     void* dTriSlot = nullptr;                    // original triangle index -> leaf-order record
     void* dNodes8 = nullptr; void* dTris8 = nullptr;   // 8-wide tree (bvh8.h)
     WfBuffers wf{};                              // wavefront path state + queues (sized by mrt_resize)
-    bool profile = false;                        // event pair around every trace launch
+    bool profile = getenv("MRT_WAVE_LOG") != nullptr;                        // event pair around every trace launch
     std::vector<cudaEvent_t> profEvents; size_t profUsed = 0;
     unsigned int* dWaveCounts = nullptr; size_t waveCountCap = 0;   // per-wave queue sizes (profile mode)
     float4* dSamples = nullptr; size_t sampleCap = 0;            // per-sample radiance of a wavefront batch
@@ -149,6 +152,8 @@ int mrt_create(const mrt_config* cfg, mrt_ctx** out) {
     if (c->cfg.bvh_max_leaf == 0) c->cfg.bvh_max_leaf = 4;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&c->ev0)); CK(cudaEventCreate(&c->ev1)); CK(cudaEventCreate(&c->evK0)); CK(cudaEventCreate(&c->evK1));
+    CK(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
+    for (int g = 0; g < 4; ++g) { CK(cudaStreamCreateWithFlags(&c->groupStream[g], cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&c->evJoin[g], cudaEventDisableTiming)); }
     for (auto& e : c->user) CK(cudaEventCreate(&e));
     CK(cudaEventCreateWithFlags(&c->tableCopied, cudaEventDisableTiming));
     CK(cudaMalloc(&c->dCounters, 4 * sizeof(unsigned long long)));
@@ -170,6 +175,8 @@ int mrt_destroy(mrt_ctx* c) {
     if (c->hFrameTable) cudaFreeHost(c->hFrameTable);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->evK0); cudaEventDestroy(c->evK1); cudaEventDestroy(c->tableCopied);
     for (auto& e : c->user) cudaEventDestroy(e);
+    for (int g = 0; g < 4; ++g) { if (c->groupStream[g]) { cudaStreamSynchronize(c->groupStream[g]); cudaStreamDestroy(c->groupStream[g]); } if (c->evJoin[g]) cudaEventDestroy(c->evJoin[g]); }
+    if (c->evFork) cudaEventDestroy(c->evFork);
     cudaStreamDestroy(c->stream);
     delete c;
     return MRT_OK;
@@ -279,7 +286,8 @@ int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
     {   // wavefront path state: one slot per pixel of an 8x4-tiled grid, SoA float4 arrays + two queue pairs
         const size_t slots = (size_t)((width + 7u) / 8u) * ((height + 3u) / 4u) * 32u;
         const size_t f4 = slots * sizeof(float4), u4 = slots * sizeof(uint32_t);
-        const size_t total = 7 * f4 + 6 * u4 + 64;
+        const size_t regions = slots / 32;                                  // smallest region = one 8x4 tile
+        const size_t total = 7 * f4 + 6 * u4 + 128 + 2 * regions * sizeof(uint32_t);      // 128 = 4 groups x (counts[4], heads[2], 2 spare)
         CK(cudaMalloc(&c->wfArena, total));
         CK(cudaMemsetAsync(c->wfArena, 0, total, c->stream));
         char* p = static_cast<char*>(c->wfArena);
@@ -289,7 +297,8 @@ int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
         c->wf.S0 = take4(); c->wf.S1 = take4();
         c->wf.visible = takeU(); c->wf.item = takeU();
         c->wf.queueExt[0] = takeU(); c->wf.queueExt[1] = takeU(); c->wf.queueShadow[0] = takeU(); c->wf.queueShadow[1] = takeU();
-        c->wf.counts = reinterpret_cast<unsigned int*>(p); c->wf.heads = c->wf.counts + 4; c->wf.workHead = c->wf.counts + 6;
+        c->wf.counts = reinterpret_cast<unsigned int*>(p); c->wf.heads = c->wf.counts + 4; p += 128;
+        c->wf.regionNext = reinterpret_cast<unsigned int*>(p); c->wf.blockRegion = c->wf.regionNext + regions;
         c->wf.slots = (uint32_t)slots; c->wf.pixels = (uint32_t)slots;
     }
     return MRT_OK;
@@ -460,7 +469,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             const uint32_t Lp = c->cfg.max_path_length;
             auto waves_for = [Lp](uint32_t nf) { return (uint64_t)nf * Lp + Lp + 2; };
             uint64_t wavesTotal = 0;
-            for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) wavesTotal += waves_for(std::min(maxSub, n_frames - f0));
+            for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) wavesTotal += 4 * waves_for(std::min(maxSub, n_frames - f0));   // x4: up to 4 slot groups
             if (c->profile) {
                 while (c->profEvents.size() < 2 * wavesTotal) { cudaEvent_t e; CK(cudaEventCreate(&e)); c->profEvents.push_back(e); }
                 if (c->waveCountCap < wavesTotal) {
@@ -469,27 +478,67 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
                     c->waveCountCap = wavesTotal;
                 }
             }
+            // Slot groups (experiment, MRT_WF_SPLIT=2..4; default 1 = off): the slots are cut into equal parts, each with its
+            // own queues and stream, so that one group's kernels could fill the SMs freed while another group's persistent
+            // trace kernel drains.  Measured on B200 (profiles/r1_k_sweep.log): 2 groups = no change, 3-4 groups 4-8 %
+            // slower — the drain tail is not what limits a wave — so the production path runs one group on one stream.
+            static const int splitEnv = getenv("MRT_WF_SPLIT") ? atoi(getenv("MRT_WF_SPLIT")) : 1;
+            uint32_t groups = (uint32_t)std::min(4, std::max(1, splitEnv));
+            while (groups > 1 && b.slots / groups < 262144u) --groups;                     // small images: not worth splitting
+            uint32_t per = ((b.slots + groups - 1u) / groups + 255u) / 256u * 256u;
+            WfBuffers gb[4];
+            for (uint32_t g = 0; g < groups; ++g) {
+                const uint32_t at = std::min(b.slots, g * per), n = std::min(per, b.slots - at);
+                WfBuffers h = b;
+                h.P0 += at; h.P1 += at; h.P2 += at; h.P3 += at; h.H += at; h.S0 += at; h.S1 += at; h.visible += at; h.item += at;
+                for (int q = 0; q < 2; ++q) { h.queueExt[q] += at; h.queueShadow[q] += at; }
+                h.counts = b.counts + 8 * g; h.heads = h.counts + 4;
+                h.slots = n; h.slotBase = at; h.allCounts = b.counts; h.groups = groups;
+                gb[g] = h;
+            }
+            b.allCounts = b.counts; b.groups = groups;
+            auto stream_of = [&](uint32_t g) { return (c->profile || groups == 1) ? c->stream : c->groupStream[g]; };
             uint64_t launched = 0, pw = 0;
             for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) {
                 const uint32_t nf = std::min(maxSub, n_frames - f0);
                 RenderParams q = p;
                 q.frames = c->dFrameTable + f0; q.nFrames = nf;
-                b.totalItems = (unsigned long long)nf * b.pixels;
-                CK(cudaMemsetAsync(b.counts, 0, 7 * sizeof(unsigned int), c->stream));     // counts[4], heads[2], workHead
-                launch_wf_shade(c->stream, q, b, 0, true, count);
+                {   // MRT_WF_REGION: 32 = per-tile counters claimed per warp (default), 256 = per shade block, 0 = one global counter
+                    static const int rsEnv = getenv("MRT_WF_REGION") ? atoi(getenv("MRT_WF_REGION")) : 32;
+                    b.regionSize = rsEnv == 32 ? 32u : (rsEnv <= 0 ? std::max(1u, b.pixels) : (uint32_t)((rsEnv + 255) / 256 * 256));
+                    b.regions = (b.pixels + b.regionSize - 1u) / b.regionSize;
+                    for (uint32_t g = 0; g < groups; ++g) { gb[g].regionSize = b.regionSize; gb[g].regions = b.regions; }
+                }
+                CK(cudaMemsetAsync(b.counts, 0, 32 * sizeof(unsigned int), c->stream));    // per group: counts[4], heads[2]
+                CK(cudaMemsetAsync(b.regionNext, 0, (size_t)b.regions * sizeof(unsigned int), c->stream));
+                const bool forked = stream_of(0) != c->stream;
+                if (forked) {
+                    CK(cudaEventRecord(c->evFork, c->stream));
+                    for (uint32_t g = 0; g < groups; ++g) CK(cudaStreamWaitEvent(c->groupStream[g], c->evFork, 0));
+                }
+                for (uint32_t g = 0; g < groups; ++g) launch_wf_shade(stream_of(g), q, gb[g], 0, true, count);
                 const uint64_t waves = waves_for(nf);
-                for (uint64_t w = 0; w < waves; ++w, ++pw) {
-                    if (c->profile) {
-                        // queue sizes of this wave (the trace kernel clears the other pair, so copy them out first)
-                        CK(cudaMemcpyAsync(c->dWaveCounts + 2 * pw, b.counts + 2 * (w & 1u), 2 * sizeof(unsigned int), cudaMemcpyDeviceToDevice, c->stream));
-                        CK(cudaEventRecord(c->profEvents[2 * pw], c->stream));
+                for (uint64_t w = 0; w < waves; ++w) {
+                    for (uint32_t g = 0; g < groups; ++g, ++pw) {
+                        cudaStream_t st = stream_of(g);
+                        if (c->profile) {
+                            // queue sizes of this wave (the trace kernel clears the other pair, so copy them out first)
+                            CK(cudaMemcpyAsync(c->dWaveCounts + 2 * pw, gb[g].counts + 2 * (w & 1u), 2 * sizeof(unsigned int), cudaMemcpyDeviceToDevice, st));
+                            CK(cudaEventRecord(c->profEvents[2 * pw], st));
+                        }
+                        launch_wf_trace(st, q, gb[g], (uint32_t)(w & 1u));
+                        if (c->profile) CK(cudaEventRecord(c->profEvents[2 * pw + 1], st));
+                        launch_wf_shade(st, q, gb[g], (uint32_t)w, false, count);
                     }
-                    launch_wf_trace(c->stream, q, b, (uint32_t)(w & 1u));
-                    if (c->profile) CK(cudaEventRecord(c->profEvents[2 * pw + 1], c->stream));
-                    launch_wf_shade(c->stream, q, b, (uint32_t)(w & 1u), false, count);
+                }
+                if (forked) {
+                    for (uint32_t g = 0; g < groups; ++g) {
+                        CK(cudaEventRecord(c->evJoin[g], c->groupStream[g]));
+                        CK(cudaStreamWaitEvent(c->stream, c->evJoin[g], 0));
+                    }
                 }
                 launch_wf_resolve_samples(c->stream, q, b);
-                launched += 2 + 2 * waves;
+                launched += 1 + groups * (1 + 2 * waves);
             }
             if (c->profile) c->profUsed = 2 * pw;
             LAUNCHED(c, launched);
@@ -603,11 +652,16 @@ int mrt_get_stats(mrt_ctx* c, mrt_stats* out) {
         std::vector<unsigned int> wc(c->profUsed);
         CK(cudaMemcpy(wc.data(), c->dWaveCounts, c->profUsed * sizeof(unsigned int), cudaMemcpyDeviceToHost));
         double sum = 0.0; uint32_t n = 0;
+        const char* logPath = getenv("MRT_WAVE_LOG");                      // diagnostic: per-wave queue sizes and trace time
+        FILE* log = logPath ? fopen(logPath, "w") : nullptr;
+        if (log) fprintf(log, "wave,extension_rays,light_rays,trace_ms\n");
         for (size_t w = 0; w < c->profUsed / 2; ++w) {
             if (wc[2 * w] + wc[2 * w + 1] == 0) continue;                 // empty wave: the kernel returned at once
             float ms = 0; CK(cudaEventElapsedTime(&ms, c->profEvents[2 * w], c->profEvents[2 * w + 1]));
             sum += ms; ++n;
+            if (log) fprintf(log, "%zu,%u,%u,%.4f\n", w, wc[2 * w], wc[2 * w + 1], ms);
         }
+        if (log) fclose(log);
         c->stats.profile_trace_ms = (float)sum; c->stats.profile_trace_launches = n;
     }
     *out = c->stats;

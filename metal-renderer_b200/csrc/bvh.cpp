@@ -15,6 +15,7 @@
 #include <chrono>
 #include <cmath>
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <mutex>
@@ -251,7 +252,9 @@ void build_bvh(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, 
 // or another wide node (cost area * 1 + its 8 children).  Leaves of the binary tree are kept whole.
 namespace {
 
-constexpr float kCostNode = 1.0f, kCostPrim = 0.3f;
+constexpr float kCostNode = 1.0f;
+// cost of one triangle test relative to one node test (8 boxes); MRT_BVH8_CPRIM overrides it for A/B sweeps
+static const float kCostPrim = getenv("MRT_BVH8_CPRIM") ? (float)atof(getenv("MRT_BVH8_CPRIM")) : 0.3f;
 constexpr uint32_t kMaxLeaf8 = 3;
 
 struct Collapse {

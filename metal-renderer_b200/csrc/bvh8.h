@@ -91,6 +91,20 @@ MRT_HD float mrt_max3(float a, float b, float c) {
     float m = a > b ? a : b; return m > c ? m : c;
 #endif
 }
+MRT_HD float mrt_min2(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return fminf(a, b);
+#else
+    return a < b ? a : b;
+#endif
+}
+MRT_HD float mrt_max2(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return fmaxf(a, b);
+#else
+    return a > b ? a : b;
+#endif
+}
 // byte j of w as the float 32768 + byte: one PRMT builds the bit pattern 0x47 00 bb 00 (an int->float conversion
 // would go through the quarter-rate XU pipe: ncu showed it 65 % busy with 48 I2F.U8 per node)
 MRT_HD float mrt_plane(uint32_t w, int j, uint32_t magic) {
@@ -151,8 +165,9 @@ MRT_HD uint32_t bvh8_hit_slots(const uint32_t* w, const Ray8& r, float tmin, flo
             const float t0x = mrt_fma(mrt_plane(nx, j, k), ax, nxc), t1x = mrt_fma(mrt_plane(fx, j, k), ax, fxc);
             const float t0y = mrt_fma(mrt_plane(ny, j, k), ay, nyc), t1y = mrt_fma(mrt_plane(fy, j, k), ay, fyc);
             const float t0z = mrt_fma(mrt_plane(nz, j, k), az, nzc), t1z = mrt_fma(mrt_plane(fz, j, k), az, fzc);
-            const float tn = mrt_max3(t0x, t0y, t0z), tf = mrt_min3(t1x, t1y, t1z);
-            if (tn <= tf && tn <= tmax && tf >= tmin) hit |= 1u << (4 * h + j);
+            // [tn, tf] clipped to [tmin, tmax] (tmin <= tmax on every live ray): one compare per child instead of three
+            const float tn = mrt_max2(mrt_max3(t0x, t0y, t0z), tmin), tf = mrt_min2(mrt_min3(t1x, t1y, t1z), tmax);
+            if (tn <= tf) hit |= 1u << (4 * h + j);
         }
     }
     return hit;

@@ -126,6 +126,7 @@ template <class IO>
 __device__ __forceinline__ void trace_persistent(const float4* __restrict__ nodes, const float4* __restrict__ tris,
                                                  uint32_t total, unsigned int* head, uint32_t refillBelow, uint32_t leafMin, IO& io) {
     const uint32_t lane = threadIdx.x & 31u;
+    leafMin &= 0xffu;                                  // upper bits tune the wide-tree kernel only (device_trace8.cuh)
     const float tiny = 1e-30f;
     bool alive = false, exhausted = (total == 0);
     uint32_t tag = 0, target = MRT_NO_HIT;

@@ -58,8 +58,9 @@ struct WfBuffers {
                          // 0 if not; written by shade: 2 = light ray queued, 3 = none
     uint32_t* item;      // work item (frame-table entry * pixels + pixel) the slot is tracing; 0xFFFFFFFF none, ..FE retry
     float4* samples;     // radiance of every finished sample of the batch: [frame-table entry][pixel]
-    unsigned int* workHead;  // next unclaimed work item
-    unsigned long long totalItems;   // nFrames * pixels
+    unsigned int* regionNext;   // per region of 256 pixels: next unclaimed item (frame-major inside the region)
+    unsigned int* blockRegion;  // per shade block: region it currently draws items from (regions = none)
+    uint32_t regions, regionSize;   // regionSize: 32 (one tile, claimed per warp), a multiple of 256, or pixels (one global counter)
     uint32_t pixels;     // owned pixels in 8x4-tiled order, padded: tilesX * tilesY * 32
     uint32_t* queueExt[2];
     uint32_t* queueShadow[2];
@@ -67,7 +68,9 @@ struct WfBuffers {
     unsigned int* heads;     // [parity] work counter of the persistent trace kernel
     const uint32_t* triSlot; // original triangle index -> record in triRecords
     const float4* triRecords;// the triangle records the trace kernel uses (wide or binary tree order)
-    uint32_t slots;          // path slots in flight (<= pixels)
+    uint32_t slots;          // path slots of this group (pointers above are already offset to the group's first slot)
+    uint32_t slotBase;       // first slot of the group in the whole slot array (multiple of 256)
+    const unsigned int* allCounts; uint32_t groups;   // every group's counts block (8 words each), for the drain check
 };
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays);
 void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave);

@@ -114,6 +114,12 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
 #define MRT_ITEM_NONE  0xFFFFFFFFu      /* slot has nothing to do (and will not get anything: work exhausted) */
 #define MRT_ITEM_RETRY 0xFFFFFFFEu      /* slot drew a padding pixel: fetch again next wave */
 
+#define WF_PROBES 8
+__device__ __forceinline__ uint32_t wf_region_pixels(uint32_t r, uint32_t regionSize, uint32_t pixels) {
+    const uint32_t at = r * regionSize;
+    return pixels - at < regionSize ? pixels - at : regionSize;
+}
+
 __device__ __forceinline__ bool wf_pixel_of(uint32_t pix, const RenderParams& P, uint32_t& x, uint32_t& y) {
     const uint32_t tilesX = (P.g.W + 7u) >> 3;
     const uint32_t tile = pix >> 5, l = pix & 31u;
@@ -124,8 +130,8 @@ __device__ __forceinline__ bool wf_pixel_of(uint32_t pix, const RenderParams& P,
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, uint32_t outParity, uint32_t first) {
-    __shared__ uint32_t sE[8], sS[8], sN[8], sW[8], sBase[3];
+__global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, uint32_t outParity, uint32_t first, uint32_t seq) {
+    __shared__ uint32_t sE[8], sS[8], sN[8], sW[8], sBase[5];
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
@@ -186,21 +192,62 @@ __global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, u
         }
     }
 
-    // ---- claim work items: one atomic per block ----
+    // ---- claim work items from the claimer's current region: one atomic per warp (regions of one 8x4 tile) or per
+    //      block (larger regions); a claimer whose region ran dry adopts a random region that still has items ----
     const unsigned mW = __ballot_sync(0xffffffffu, need);
-    if (lane == 0) sW[warp] = __popc(mW);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t a = 0;
-        for (int w = 0; w < 8; ++w) { uint32_t n = sW[w]; sW[w] = a; a += n; }
-        sBase[2] = a ? atomicAdd(b.workHead, a) : 0u;
+    const uint32_t R = b.regions, nf = P.nFrames, rs = b.regionSize;
+    uint32_t jBase = 0, jLim = 0, jCur = 0, rank = __popc(mW & lt);
+    auto claim = [&](uint32_t claimer, uint32_t own, uint32_t a) {
+        uint32_t cur = first ? own : b.blockRegion[claimer], base = 0, lim = 0;
+        if (cur < R) {
+            lim = wf_region_pixels(cur, rs, b.pixels) * nf;
+            base = atomicAdd(b.regionNext + cur, a);
+        }
+        if (base >= lim) {
+            cur = R; base = lim = 0;
+            uint32_t h = (claimer + 1u) * 0x9E3779B1u + seq * 0x85EBCA77u;
+            uint32_t cand[WF_PROBES], left[WF_PROBES];
+#pragma unroll
+            for (int t = 0; t < WF_PROBES; ++t) {
+                h = h * 0x2C1B3C6Du + 0x297A2D39u;
+                cand[t] = (uint32_t)(((unsigned long long)(h ^ (h >> 15)) * R) >> 32);
+                left[t] = *(volatile unsigned int*)(b.regionNext + cand[t]);
+            }
+#pragma unroll
+            for (int t = 0; t < WF_PROBES; ++t) {
+                const uint32_t l = wf_region_pixels(cand[t], rs, b.pixels) * nf;
+                if (cur == R && left[t] < l) {
+                    const uint32_t got = atomicAdd(b.regionNext + cand[t], a);
+                    if (got < l) { cur = cand[t]; base = got; lim = l; }
+                }
+            }
+        }
+        b.blockRegion[claimer] = cur;
+        jBase = base; jLim = lim; jCur = cur;
+    };
+    if (rs == 32u) {
+        if (mW) {
+            if (lane == 0) claim((b.slotBase + slot) >> 5, (b.slotBase + slot) >> 5, __popc(mW));
+            jBase = __shfl_sync(0xffffffffu, jBase, 0); jLim = __shfl_sync(0xffffffffu, jLim, 0); jCur = __shfl_sync(0xffffffffu, jCur, 0);
+        }
+    } else {
+        if (lane == 0) sW[warp] = __popc(mW);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t a = 0;
+            for (int w = 0; w < 8; ++w) { uint32_t n = sW[w]; sW[w] = a; a += n; }
+            if (a) claim(blockIdx.x + b.slotBase / 256u, (uint32_t)(((unsigned long long)blockIdx.x * 256u + b.slotBase) / rs), a);
+            sBase[2] = jBase; sBase[3] = jLim; sBase[4] = jCur;
+        }
+        __syncthreads();
+        jBase = sBase[2]; jLim = sBase[3]; jCur = sBase[4]; rank += sW[warp];
     }
-    __syncthreads();
     if (need) {
-        const unsigned long long w = (unsigned long long)sBase[2] + sW[warp] + __popc(mW & lt);
-        if (w < b.totalItems) {
-            item = (uint32_t)w;
-            const uint32_t k = item / b.pixels, pix = item - k * b.pixels;
+        const uint32_t j = jBase + rank;
+        item = MRT_ITEM_RETRY;                             // nothing this wave (region ran dry, or a padding pixel)
+        if (j < jLim) {
+            const uint32_t rp = wf_region_pixels(jCur, rs, b.pixels);
+            const uint32_t k = j / rp, pix = jCur * rs + (j - k * rp);
             uint32_t x, y;
             if (wf_pixel_of(pix, P, x, y)) {
                 const uint4 e = __ldg(P.frames + k);
@@ -208,11 +255,8 @@ __global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, u
                 const uint32_t t = s == 0 ? e.y : (s == 1 ? e.z : e.w);
                 ray_generator(st, P.noisePool + t * tileStride, x, y, P.g.W, P.g.H);   // Renderer.mm:508-512
                 pushE = true;
-            } else {
-                item = MRT_ITEM_RETRY;                     // padding pixel of the 8x4 tiling
+                item = k * b.pixels + pix;
             }
-        } else {
-            item = MRT_ITEM_NONE;
         }
     }
     if (valid) {
@@ -247,9 +291,12 @@ __global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, u
 __global__ void __launch_bounds__(256) k_wf_resolve_samples(RenderParams P, WfBuffers b) {
     const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
     if (pix == 0) {     // every item must have been claimed and both queue pairs drained (api.cu checks this word)
-        const unsigned int left = b.counts[0] + b.counts[1] + b.counts[2] + b.counts[3] + (*b.workHead < b.totalItems ? 1u : 0u);
+        unsigned int left = 0;
+        for (uint32_t g = 0; g < b.groups; ++g) left += b.allCounts[8 * g] + b.allCounts[8 * g + 1] + b.allCounts[8 * g + 2] + b.allCounts[8 * g + 3];
         if (left) b.counts[7] = left;
     }
+    if (pix < b.pixels && (pix % b.regionSize) == 0u &&
+        b.regionNext[pix / b.regionSize] < wf_region_pixels(pix / b.regionSize, b.regionSize, b.pixels) * P.nFrames) b.counts[7] = 1u;
     uint32_t x, y;
     if (pix >= b.pixels || !wf_pixel_of(pix, P, x, y)) return;
     const uint32_t at = y * P.g.W + x;
@@ -270,11 +317,11 @@ static int device_sms() {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     return n > 0 ? n : 148;
 }
-struct TraceTuning { int minb, refill, leafMin, wide; };
+struct TraceTuning { int minb, refill, leafMin, wide, triRatio, prefetch; };
 static TraceTuning trace_tuning() {
     static const int wide = env_int("MRT_BVH_WIDTH", 8) == 8 ? 1 : 0;
     static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", wide ? 8 : 10), env_int("MRT_TRACE_REFILL", 24),
-                                   env_int("MRT_TRACE_LEAFMIN", 8), wide };
+                                   env_int("MRT_TRACE_LEAFMIN", 8), wide, env_int("MRT_TRACE_TRIRATIO", 0), env_int("MRT_TRACE_PREFETCH", 0) };
     return t;
 }
 
@@ -287,7 +334,8 @@ void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const voi
     const char* r = static_cast<const char*>(rays);
     const uint32_t warpsNeeded = (count + 31u) / 32u;
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
-    const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin));
+    const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin)) |
+                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8) | (t.prefetch ? 1u << 16 : 0u);
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); uint32_t need = (warpsNeeded + 3u) / 4u; return need < cap ? need : cap; };
 #define MRT_LAUNCH_ISECT(MB, WD) k_intersect_persistent<MB, WD><<<blocks(MB), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin, 0x47000000u)
     if (t.wide) {
@@ -303,7 +351,8 @@ void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const voi
 void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave) {
     const TraceTuning t = trace_tuning();
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
-    const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin));
+    const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin)) |
+                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8) | (t.prefetch ? 1u << 16 : 0u);
     const uint32_t parity = wave & 1u;
     const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
@@ -327,8 +376,8 @@ void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     if (b.slots == 0) return;
     const uint32_t blocks = (b.slots + 255u) / 256u;
     const uint32_t outParity = first ? 0u : ((wave + 1u) & 1u);               // shade(w) fills the queues trace(w+1) consumes
-    if (countRays) k_wf_shade<true><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u);
-    else           k_wf_shade<false><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u);
+    if (countRays) k_wf_shade<true><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
+    else           k_wf_shade<false><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
 }
 
 bool trace_uses_wide_bvh() { return trace_tuning().wide != 0; }
