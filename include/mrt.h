@@ -133,6 +133,7 @@ int mrt_set_scene_from(mrt_ctx* ctx, const mrt_scene* scene);
  * Intersection / image for width x height rays, zero-fill, restart accumulation.  width/height are
  * the DISPATCH size (the reference's CONTENT_SCALE x drawable size). */
 int mrt_resize(mrt_ctx* ctx, uint32_t width, uint32_t height);
+int mrt_get_size(mrt_ctx* ctx, uint32_t* width, uint32_t* height);   /* 0 x 0 before the first mrt_resize */
 
 /* Noise slot upload (Renderer.mm:115-129 initial fill, 492-496 per-frame refresh).
  * slot in [0,3); tile = 64*64 float4 in [0,1). */
@@ -196,6 +197,29 @@ int mrt_read_buffer(mrt_ctx* ctx, uint32_t which, void* dst, size_t bytes);
 int mrt_write_buffer(mrt_ctx* ctx, uint32_t which, const void* src, size_t bytes);
 int mrt_get_stats(mrt_ctx* ctx, mrt_stats* out);
 int mrt_reset_stats(mrt_ctx* ctx);
+
+/* ---- presentation pass and checkpoint: the callers' side of the path ---- */
+/* blitFragment (Shaders.metal:33-69) on the headless image: tone mapping 1-exp(-c) (ENABLE_TONE_MAPPING,
+ * Raytracing.h:11), manual sRGB encode (MANUAL_SRGB, Raytracing.h:12; toSRGB Raytracing.h:130-135) and the comparison
+ * modes of Raytracing.h:27-33 against a reference image (nearest texel, any size; Renderer.mm:160-250 loads it).
+ * The macros of the reference are run-time parameters here; mrt_display_params_default gives the reference's values. */
+typedef struct mrt_display_params {
+    uint32_t tone_mapping;      /* 0 / 1 */
+    uint32_t manual_srgb;       /* 0 / 1 */
+    uint32_t comparison_mode;   /* MRT_COMPARE_* (mrt_abi.h) */
+    float comparison_scale;     /* COMPARISON_SCALE */
+} mrt_display_params;
+void mrt_display_params_default(mrt_display_params* p);
+/* out_rgba: width*height*4 floats (host), row 0 = bottom.  reference_rgba: ref_width*ref_height*4 floats (host or
+ * device), row 0 = bottom, or NULL (comparison disabled whatever the mode). */
+int mrt_display(mrt_ctx* ctx, const mrt_display_params* params, const float* reference_rgba, uint32_t ref_width,
+                uint32_t ref_height, float* out_rgba);
+
+/* Accumulation checkpoint: image, size, frames accumulated, accumulate mode and the three noise slots — what a long
+ * progressive render needs to continue bit-exactly in another process (the reference only has the stub
+ * -saveCurrentImage, Renderer.mm:626-629, 659-662).  load resizes the context to the stored size. */
+int mrt_checkpoint_save(mrt_ctx* ctx, const char* path);
+int mrt_checkpoint_load(mrt_ctx* ctx, const char* path, uint32_t* frames_accumulated);
 
 /* Stand-alone replacement of one MPSRayIntersector encode (Renderer.mm:464-469, 519-523): `rays`
  * is a HOST array of `count` records of `stride_bytes` each whose first 32 bytes are

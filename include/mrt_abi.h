@@ -28,6 +28,13 @@ extern "C" {
 #define MRT_MAX_PATH_LENGTH    8            /* Raytracing.h:23 (default; runtime parameter here) */
 #define MRT_NOISE_TILE_FLOATS  (4 * MRT_NOISE_DIMENSIONS * MRT_NOISE_DIMENSIONS)
 #define MRT_NOT_A_LIGHT        0xFFFFFFFFu  /* uint32_t(-1), Renderer.mm:393 */
+/* comparison modes of the presentation pass, Raytracing.h:27-31 */
+#define MRT_COMPARE_DISABLED        0
+#define MRT_COMPARE_ABSOLUTE_VALUE  1          /* |color - ref| */
+#define MRT_COMPARE_REF_TO_COLOR    2          /* visible where the output is darker than the reference */
+#define MRT_COMPARE_COLOR_TO_REF    3          /* visible where the reference is darker than the output */
+#define MRT_COMPARE_LUMINANCE       4          /* red: output brighter, green: reference brighter */
+#define MRT_COMPARISON_SCALE        10.0f      /* Raytracing.h:33 */
 
 /* Material kinds (Raytracing.h:35-43). */
 enum {

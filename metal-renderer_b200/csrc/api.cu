@@ -62,6 +62,7 @@ struct mrt_ctx {
     void* dTriSlot = nullptr;                    // original triangle index -> leaf-order record
     void* dNodes8 = nullptr; void* dTris8 = nullptr;   // 8-wide tree (bvh8.h)
     WfBuffers wf{};                              // wavefront path state + queues (sized by mrt_resize)
+    uint32_t nextFrame = 0;                      // frame index after the last one accumulated (checkpoint)
     bool profile = getenv("MRT_WAVE_LOG") != nullptr;                        // event pair around every trace launch
     std::vector<cudaEvent_t> profEvents; size_t profUsed = 0;
     unsigned int* dWaveCounts = nullptr; size_t waveCountCap = 0;   // per-wave queue sizes (profile mode)
@@ -304,6 +305,12 @@ int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
     return MRT_OK;
 }
 
+int mrt_get_size(mrt_ctx* c, uint32_t* width, uint32_t* height) {
+    NEED(c && width && height, MRT_E_INVALID, "NULL argument");
+    *width = c->dImage ? c->W : 0; *height = c->dImage ? c->H : 0;
+    return MRT_OK;
+}
+
 int mrt_set_noise(mrt_ctx* c, uint32_t slot, const float* tile) {
     NEED(c && tile, MRT_E_INVALID, "NULL argument");
     NEED(slot < MRT_NOISE_SLOTS, MRT_E_INVALID, "slot %u out of range", slot);
@@ -383,6 +390,7 @@ int mrt_accumulate(mrt_ctx* c, uint32_t frame_index) {
     NEED_READY(c);
     launch_accumulate(c->stream, c->dImage, c->dRays, frame_index, c->cfg.accumulate_mode, c->grid());
     LAUNCHED(c, 1);
+    c->nextFrame = frame_index + 1;
     return MRT_OK;
 }
 
@@ -550,6 +558,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             if (slotTile[s] != s) CK(cudaMemcpyAsync(c->dNoisePool + s * kTileFloat4, c->dNoisePool + slotTile[s] * kTileFloat4, kTileBytes,
                                                      cudaMemcpyDeviceToDevice, c->stream));
         c->stats.frames_rendered += n_frames;
+        c->nextFrame = first_frame + span;
     }
     CK(cudaEventRecord(c->ev1, c->stream));
     c->timed = true;
@@ -592,6 +601,89 @@ int mrt_scale_image(mrt_ctx* c, float scale) {
     LAUNCHED(c, 1);
     return MRT_OK;
 }
+void mrt_display_params_default(mrt_display_params* p) {
+    if (!p) return;
+    p->tone_mapping = 0; p->manual_srgb = 0;                       // Raytracing.h:11-12
+    p->comparison_mode = MRT_COMPARE_DISABLED; p->comparison_scale = MRT_COMPARISON_SCALE;   // Raytracing.h:32-33
+}
+
+int mrt_display(mrt_ctx* c, const mrt_display_params* params, const float* reference_rgba, uint32_t ref_width, uint32_t ref_height,
+                float* out_rgba) {
+    NEED(c && params && out_rgba, MRT_E_INVALID, "NULL argument");
+    NEED(c->dImage, MRT_E_STATE, "no size: call mrt_resize first");
+    NEED(params->comparison_mode <= MRT_COMPARE_LUMINANCE, MRT_E_INVALID, "comparison mode %u out of range", params->comparison_mode);
+    NEED(reference_rgba == nullptr || (ref_width >= 1 && ref_height >= 1), MRT_E_INVALID, "reference image without a size");
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t n = (size_t)c->W * c->H;
+    float4 *dOut = nullptr, *dRef = nullptr;
+    CK(cudaMalloc(&dOut, n * sizeof(float4)));
+    cudaError_t e = cudaSuccess;
+    if (reference_rgba) {
+        const size_t rb = (size_t)ref_width * ref_height * sizeof(float4);
+        e = cudaMalloc(&dRef, rb);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dRef, reference_rgba, rb, cudaMemcpyDefault, c->stream);
+    }
+    if (e == cudaSuccess) {
+        launch_display(c->stream, c->dImage, dRef, dOut, c->W, c->H, ref_width, ref_height, params->tone_mapping, params->manual_srgb,
+                       params->comparison_mode, params->comparison_scale);
+        LAUNCHED(c, 1);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_rgba, dOut, n * sizeof(float4), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(dOut); cudaFree(dRef);
+    CK(e);
+    return MRT_OK;
+}
+
+// ---- checkpoint: "MRTCKPT1", W, H, nextFrame, accumulate mode, image, the three noise slots ------------------------
+static const char kCkptMagic[8] = {'M', 'R', 'T', 'C', 'K', 'P', 'T', '1'};
+
+int mrt_checkpoint_save(mrt_ctx* c, const char* path) {
+    NEED(c && path, MRT_E_INVALID, "NULL argument");
+    NEED(c->dImage, MRT_E_STATE, "no size: call mrt_resize first");
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t n = (size_t)c->W * c->H;
+    std::vector<float> image(4 * n), noise((size_t)MRT_NOISE_SLOTS * MRT_NOISE_TILE_FLOATS);
+    CK(cudaMemcpyAsync(image.data(), c->dImage, n * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(noise.data(), c->dNoisePool, noise.size() * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    FILE* f = fopen(path, "wb");
+    NEED(f, MRT_E_IO, "cannot open %s for writing", path);
+    const uint32_t head[4] = {c->W, c->H, c->nextFrame, c->cfg.accumulate_mode};
+    bool ok = fwrite(kCkptMagic, 1, 8, f) == 8 && fwrite(head, sizeof head, 1, f) == 1 &&
+              fwrite(image.data(), sizeof(float), image.size(), f) == image.size() &&
+              fwrite(noise.data(), sizeof(float), noise.size(), f) == noise.size();
+    ok = (fclose(f) == 0) && ok;
+    NEED(ok, MRT_E_IO, "short write to %s", path);
+    return MRT_OK;
+}
+
+int mrt_checkpoint_load(mrt_ctx* c, const char* path, uint32_t* frames_accumulated) {
+    NEED(c && path, MRT_E_INVALID, "NULL argument");
+    FILE* f = fopen(path, "rb");
+    NEED(f, MRT_E_IO, "cannot open %s", path);
+    char magic[8]; uint32_t head[4] = {0, 0, 0, 0};
+    bool ok = fread(magic, 1, 8, f) == 8 && memcmp(magic, kCkptMagic, 8) == 0 && fread(head, sizeof head, 1, f) == 1;
+    ok = ok && head[0] >= 2 && head[1] >= 2 && (uint64_t)head[0] * head[1] < (1ull << 31) && head[3] <= MRT_ACCUM_REPLACE;
+    std::vector<float> image, noise((size_t)MRT_NOISE_SLOTS * MRT_NOISE_TILE_FLOATS);
+    if (ok) {
+        image.resize((size_t)4 * head[0] * head[1]);
+        ok = fread(image.data(), sizeof(float), image.size(), f) == image.size() &&
+             fread(noise.data(), sizeof(float), noise.size(), f) == noise.size();
+    }
+    fclose(f);
+    NEED(ok, MRT_E_IO, "%s is not a complete checkpoint", path);
+    if (c->W != head[0] || c->H != head[1] || !c->dImage) { int rc = mrt_resize(c, head[0], head[1]); if (rc != MRT_OK) return rc; }
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(c->dImage, image.data(), image.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->dNoisePool, noise.data(), noise.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->nextFrame = head[2]; c->cfg.accumulate_mode = head[3];
+    if (frames_accumulated) *frames_accumulated = head[2];
+    return MRT_OK;
+}
+
 int mrt_clear_image(mrt_ctx* c) {
     NEED(c && c->dImage, MRT_E_STATE, "no image");
     CK(cudaSetDevice(c->cfg.device));

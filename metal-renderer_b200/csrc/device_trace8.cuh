@@ -30,10 +30,10 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
     const uint32_t lane = threadIdx.x & 31u;
     const float tiny = 1e-30f;
     // leafMin carries the vote tuning: bits 0-7 = lanes with triangles that force a triangle step, bits 8-15 = ratio r
-    // (triangle step as soon as 16 * lanes-with-triangles >= r * lanes-with-node-work; 0 = off), bit 16 = L1 prefetch of
-    // the first triangle when a node step finds a leaf
+    // (triangle step as soon as 16 * lanes-with-triangles >= r * lanes-with-node-work; 0 = off).  A triangle step
+    // costs ~0.4 node steps, so r = 6 picks whichever step advances more lanes per instruction (pass M: +2 %; an L1
+    // prefetch of the leaf's first triangle at the end of the node step was tried there too and lost 1-20 %).
     const int triRatio = int((leafMin >> 8) & 0xffu);
-    const bool prefetchTri = ((leafMin >> 16) & 1u) != 0u;
     leafMin &= 0xffu;
     bool alive = false, exhausted = (total == 0);
     uint32_t tag = 0, target = MRT_NO_HIT;
@@ -107,11 +107,6 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
                     const uint32_t imask = w[3] >> 24;
                     gx = w[4]; gy = ((hs & imask) << 24) | imask;
                     tx = w[5]; ty = bvh8_triangle_mask(w[6], w[7], hs & ~imask);
-                    if (prefetchTri && ty != 0) {
-                        const float4* tp = tris + 3 * (size_t)(tx + uint32_t(__ffs(ty) - 1));
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(tp));
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(tp + 2));
-                    }
                     if (ty == 0 && !(gy & 0xff000000u)) {                       // nothing hit below: next group or done
                         if (sp > 0) { uint2 e = stack[--sp]; gx = e.x; gy = e.y; }
                         else { if (best.tri == MRT_NO_HIT) best.t = -1.0f; io.store(tag, target, best); alive = false; }

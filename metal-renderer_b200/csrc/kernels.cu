@@ -128,6 +128,46 @@ __global__ void __launch_bounds__(256) k_scale_image(float4* __restrict__ image,
     image[i] = make_float4(c.x * scale, c.y * scale, c.z * scale, 1.0f);
 }
 
+// ---- presentation pass: blitFragment (Shaders.metal:33-69) as a compute kernel over a headless RGBA32F buffer ----
+// One thread per output pixel; the output has the image's size, so the nearest sample of the image is the pixel
+// itself and the reference (any size) is read at its nearest texel.  toSRGB = Raytracing.h:130-135.
+__device__ __forceinline__ float to_srgb(float v) {
+    if (v <= 0.0f) return 0.0f;
+    if (v >= 1.0f) return 1.0f;
+    return (v < 0.0031308f) ? (12.92f * v) : (1.055f * powf(v, 1.0f / 2.4f) - 0.055f);
+}
+__device__ __forceinline__ uint32_t nearest_texel(uint32_t i, uint32_t n, uint32_t m) {
+    const float u = __fdiv_rn(float(i) + 0.5f, float(n));
+    const uint32_t t = uint32_t(u * float(m));
+    return t < m ? t : m - 1u;
+}
+__global__ void __launch_bounds__(256) k_display(const float4* __restrict__ image, const float4* __restrict__ ref,
+                                                 float4* __restrict__ out, uint32_t W, uint32_t H, uint32_t RW, uint32_t RH,
+                                                 uint32_t toneMapping, uint32_t manualSRGB, uint32_t mode, float scale) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= W * H) return;
+    const uint32_t x = i % W, y = i / W;
+    float4 c = image[i];
+    if (toneMapping) c = make_float4(1.0f - expf(-c.x), 1.0f - expf(-c.y), 1.0f - expf(-c.z), 1.0f - expf(-c.w));
+    if (manualSRGB) { c.x = to_srgb(c.x); c.y = to_srgb(c.y); c.z = to_srgb(c.z); }
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ref == nullptr) mode = MRT_COMPARE_DISABLED;
+    if (mode != MRT_COMPARE_DISABLED) r = ref[(size_t)nearest_texel(y, H, RH) * RW + nearest_texel(x, W, RW)];
+    float4 o = c;
+    if (mode == MRT_COMPARE_ABSOLUTE_VALUE)
+        o = make_float4(fabsf(c.x - r.x) * scale, fabsf(c.y - r.y) * scale, fabsf(c.z - r.z) * scale, fabsf(c.w - r.w) * scale);
+    else if (mode == MRT_COMPARE_REF_TO_COLOR)
+        o = make_float4(fmaxf(0.0f, r.x - c.x) * scale, fmaxf(0.0f, r.y - c.y) * scale, fmaxf(0.0f, r.z - c.z) * scale, fmaxf(0.0f, r.w - c.w) * scale);
+    else if (mode == MRT_COMPARE_COLOR_TO_REF)
+        o = make_float4(fmaxf(0.0f, c.x - r.x) * scale, fmaxf(0.0f, c.y - r.y) * scale, fmaxf(0.0f, c.z - r.z) * scale, fmaxf(0.0f, c.w - r.w) * scale);
+    else if (mode == MRT_COMPARE_LUMINANCE) {
+        const float third = 1.0f / 3.0f;
+        const float lc = dot(mk3(c.x, c.y, c.z), mk3(third, third, third)), lr = dot(mk3(r.x, r.y, r.z), mk3(third, third, third));
+        o = make_float4(fmaxf(0.0f, lc - lr) * scale, fmaxf(0.0f, lr - lc) * scale, 0.0f * scale, 1.0f * scale);
+    }
+    out[i] = o;
+}
+
 // ---- fused megakernel ----------------------------------------------------------------------------------------
 // One thread owns one pixel for every frame of the batch; a warp owns an 8x4 pixel tile.  Per lane a small state
 // machine runs GEN -> (PRIMARY -> [SHADOW])* -> GEN ...: a lane whose sample ends (path died or reached
@@ -247,6 +287,10 @@ void launch_accumulate(cudaStream_t s, float4* image, const mrt_ray* rays, uint3
 }
 void launch_scale_image(cudaStream_t s, float4* image, float scale, uint32_t count) {
     k_scale_image<<<blocks_for(count), 256, 0, s>>>(image, scale, count);
+}
+void launch_display(cudaStream_t s, const float4* image, const float4* ref, float4* out, uint32_t W, uint32_t H, uint32_t RW,
+                    uint32_t RH, uint32_t toneMapping, uint32_t manualSRGB, uint32_t mode, float scale) {
+    k_display<<<blocks_for(W * H), 256, 0, s>>>(image, ref, out, W, H, RW, RH, toneMapping, manualSRGB, mode, scale);
 }
 void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays) {
     uint32_t tilesX = (p.g.W + 7u) >> 3, tilesY = (p.ownedRows + 3u) >> 2;

@@ -36,6 +36,9 @@ void launch_shadow_resolve(cudaStream_t s, const mrt_intersection* isects, mrt_r
                            const mrt_light_sampling_ray* lightRays, Grid2D g);
 void launch_accumulate(cudaStream_t s, float4* image, const mrt_ray* rays, uint32_t frameIndex, uint32_t mode, Grid2D g);
 void launch_scale_image(cudaStream_t s, float4* image, float scale, uint32_t count);
+// presentation pass (Shaders.metal:33-69); ref may be null (comparison disabled)
+void launch_display(cudaStream_t s, const float4* image, const float4* ref, float4* out, uint32_t W, uint32_t H, uint32_t RW,
+                    uint32_t RH, uint32_t toneMapping, uint32_t manualSRGB, uint32_t mode, float scale);
 
 // persistent (dynamic-fetch) form of launch_intersect: same arguments and results; `head` = zeroed work counter
 void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const void* rays, uint32_t strideBytes, uint32_t count,

@@ -129,8 +129,8 @@ __device__ __forceinline__ bool wf_pixel_of(uint32_t pix, const RenderParams& P,
     return x < P.g.W && row < P.ownedRows;
 }
 
-template <bool COUNT>
-__global__ void __launch_bounds__(256) k_wf_shade(RenderParams P, WfBuffers b, uint32_t outParity, uint32_t first, uint32_t seq) {
+template <bool COUNT, int MINB>
+__global__ void __launch_bounds__(256, MINB) k_wf_shade(RenderParams P, WfBuffers b, uint32_t outParity, uint32_t first, uint32_t seq) {
     __shared__ uint32_t sE[8], sS[8], sN[8], sW[8], sBase[5];
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -317,11 +317,11 @@ static int device_sms() {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     return n > 0 ? n : 148;
 }
-struct TraceTuning { int minb, refill, leafMin, wide, triRatio, prefetch; };
+struct TraceTuning { int minb, refill, leafMin, wide, triRatio; };
 static TraceTuning trace_tuning() {
     static const int wide = env_int("MRT_BVH_WIDTH", 8) == 8 ? 1 : 0;
     static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", wide ? 8 : 10), env_int("MRT_TRACE_REFILL", 24),
-                                   env_int("MRT_TRACE_LEAFMIN", 8), wide, env_int("MRT_TRACE_TRIRATIO", 0), env_int("MRT_TRACE_PREFETCH", 0) };
+                                   env_int("MRT_TRACE_LEAFMIN", 8), wide, env_int("MRT_TRACE_TRIRATIO", 6) };
     return t;
 }
 
@@ -335,7 +335,7 @@ void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const voi
     const uint32_t warpsNeeded = (count + 31u) / 32u;
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
     const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin)) |
-                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8) | (t.prefetch ? 1u << 16 : 0u);
+                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8);
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); uint32_t need = (warpsNeeded + 3u) / 4u; return need < cap ? need : cap; };
 #define MRT_LAUNCH_ISECT(MB, WD) k_intersect_persistent<MB, WD><<<blocks(MB), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin, 0x47000000u)
     if (t.wide) {
@@ -352,7 +352,7 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     const TraceTuning t = trace_tuning();
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
     const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin)) |
-                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8) | (t.prefetch ? 1u << 16 : 0u);
+                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8);
     const uint32_t parity = wave & 1u;
     const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
@@ -376,8 +376,16 @@ void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     if (b.slots == 0) return;
     const uint32_t blocks = (b.slots + 255u) / 256u;
     const uint32_t outParity = first ? 0u : ((wave + 1u) & 1u);               // shade(w) fills the queues trace(w+1) consumes
-    if (countRays) k_wf_shade<true><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
-    else           k_wf_shade<false><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
+    // MRT_SHADE_MINBLOCKS: 4 (default) = 64 registers with a 56-byte spill frame, 3 = 80 registers; the kernel is
+    // latency-bound (ncu pass O: 36 % warps active, long scoreboard), so occupancy wins: +3.6 % per step in pass P
+    static const int minb = env_int("MRT_SHADE_MINBLOCKS", 4);
+    if (minb >= 4) {
+        if (countRays) k_wf_shade<true, 4><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
+        else           k_wf_shade<false, 4><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
+    } else {
+        if (countRays) k_wf_shade<true, 3><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
+        else           k_wf_shade<false, 3><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
+    }
 }
 
 bool trace_uses_wide_bvh() { return trace_tuning().wide != 0; }
@@ -387,7 +395,7 @@ int wf_kernel_info(int* traceRegs, int* traceBlocksPerSM, int* shadeRegs) {
     cudaError_t e = cudaFuncGetAttributes(&a, k_wf_trace<8, 1>);
     if (e != cudaSuccess) return (int)e;
     *traceRegs = a.numRegs;
-    e = cudaFuncGetAttributes(&a, k_wf_shade<true>);
+    e = cudaFuncGetAttributes(&a, k_wf_shade<true, 3>);
     if (e != cudaSuccess) return (int)e;
     *shadeRegs = a.numRegs;
     return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(traceBlocksPerSM, k_wf_trace<8, 1>, 128, 0);

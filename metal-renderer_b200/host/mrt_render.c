@@ -8,6 +8,9 @@
  *
  * usage: mrt_render [--scene NAME|file.obj] [--size WxH] [--frames N] [--depth L] [--seed S] [--device D]
  *                   [--pipeline auto|wavefront|fused|staged] [--out image.pfm]
+ *                   [--tone] [--srgb]            presentation pass on the written image (Shaders.metal:43-51)
+ *                   [--resume file.ckpt]         continue an earlier render (frames then count from the stored index)
+ *                   [--checkpoint file.ckpt]     save image + frame index + noise slots after rendering
  */
 #define _POSIX_C_SOURCE 200809L
 #include <stdio.h>
@@ -33,6 +36,9 @@ static int write_pfm(const char* path, const float* rgba, unsigned w, unsigned h
 int main(int argc, char** argv) {
     const char* scene_name = "cornell";
     const char* out = NULL;
+    const char* resume = NULL;
+    const char* checkpoint = NULL;
+    unsigned tone = 0, srgb = 0, first = 0;
     unsigned w = 256, h = 256, frames = 16, depth = MRT_MAX_PATH_LENGTH, device = 0, pipeline = MRT_PIPELINE_AUTO;
     unsigned long long seed = 1;
     for (int i = 1; i < argc; ++i) {
@@ -50,6 +56,10 @@ int main(int argc, char** argv) {
             ++i;
         }
         else if (!strcmp(a, "--out")) { out = v; ++i; }
+        else if (!strcmp(a, "--resume")) { resume = v; ++i; }
+        else if (!strcmp(a, "--checkpoint")) { checkpoint = v; ++i; }
+        else if (!strcmp(a, "--tone")) tone = 1;
+        else if (!strcmp(a, "--srgb")) srgb = 1;
         else { fprintf(stderr, "unknown argument %s\n", a); return 2; }
     }
 
@@ -70,17 +80,21 @@ int main(int argc, char** argv) {
     CHECK(mrt_set_scene_from(ctx, scene));
     CHECK(mrt_resize(ctx, w, h));
 
+    if (resume) {                                                /* restores size, image, frame index and noise slots */
+        CHECK(mrt_checkpoint_load(ctx, resume, &first));
+        CHECK(mrt_get_size(ctx, &w, &h));
+    }
     float* tiles = (float*)malloc((size_t)(frames ? frames : 1) * MRT_NOISE_TILE_FLOATS * sizeof(float));
     float* init = (float*)malloc(MRT_NOISE_TILE_FLOATS * sizeof(float));
     float* image = (float*)malloc((size_t)w * h * 4 * sizeof(float));
     if (!tiles || !init || !image) { fprintf(stderr, "out of memory\n"); return 1; }
     mrt_noise_fill(seed, 0xFFFFFFFFu, init);                     /* all three slots start identical, Renderer.mm:115-126 */
-    for (unsigned s = 0; s < MRT_NOISE_SLOTS; ++s) CHECK(mrt_set_noise(ctx, s, init));
-    for (unsigned f = 0; f < frames; ++f) mrt_noise_fill(seed, f, tiles + (size_t)f * MRT_NOISE_TILE_FLOATS);
+    for (unsigned s = 0; s < MRT_NOISE_SLOTS && !resume; ++s) CHECK(mrt_set_noise(ctx, s, init));
+    for (unsigned f = 0; f < frames; ++f) mrt_noise_fill(seed, first + f, tiles + (size_t)f * MRT_NOISE_TILE_FLOATS);
     CHECK(mrt_sync(ctx));
 
     double t0 = now_s();
-    CHECK(mrt_render_frames(ctx, 0, frames, 1, tiles));
+    CHECK(mrt_render_frames(ctx, first, frames, 1, tiles));
     CHECK(mrt_read_image(ctx, image));
     double t1 = now_s();
 
@@ -94,6 +108,13 @@ int main(int argc, char** argv) {
            samples / (st.last_render_ms * 1e3), (double)(st.primary_rays + st.shadow_rays) / (st.last_render_ms * 1e3),
            (unsigned long long)st.primary_rays, (unsigned long long)st.shadow_rays, (unsigned long long)st.kernel_launches,
            st.bvh_nodes, st.bvh_depth, st.bvh_build_ms);
+    if (checkpoint) CHECK(mrt_checkpoint_save(ctx, checkpoint));
+    if (out && (tone || srgb)) {
+        mrt_display_params dp;
+        mrt_display_params_default(&dp);
+        dp.tone_mapping = tone; dp.manual_srgb = srgb;
+        CHECK(mrt_display(ctx, &dp, NULL, 0, 0, image));
+    }
     if (out && write_pfm(out, image, w, h)) { fprintf(stderr, "cannot write %s\n", out); return 1; }
 
     free(tiles); free(init); free(image);

@@ -33,6 +33,7 @@ NOT_A_LIGHT = 0xFFFFFFFF
 MATERIAL_DIFFUSE, MATERIAL_MIRROR, MATERIAL_SMOOTH_PLASTIC, MATERIAL_SMOOTH_DIELECTRIC = range(4)
 PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_STAGED = range(4)
 ACCUM_MEAN, ACCUM_SUM, ACCUM_REPLACE = range(3)
+COMPARE_DISABLED, COMPARE_ABSOLUTE_VALUE, COMPARE_REF_TO_COLOR, COMPARE_COLOR_TO_REF, COMPARE_LUMINANCE = range(5)   # Raytracing.h:27-31
 BUF_RAYS, BUF_LIGHT_RAYS, BUF_INTERSECTIONS, BUF_IMAGE = range(4)
 BUFFER_DTYPES = {BUF_RAYS: RAY, BUF_LIGHT_RAYS: LIGHT_RAY, BUF_INTERSECTIONS: INTERSECTION}
 
@@ -65,6 +66,12 @@ class BvhReport(C.Structure):
     _fields_ = [("nodes", C.c_uint32), ("depth", C.c_uint32), ("triangles", C.c_uint32), ("mismatches", C.c_uint32),
                 ("sah_cost", C.c_float), ("build_ms", C.c_float), ("nodes_per_ray", C.c_float),
                 ("triangles_per_ray", C.c_float)]
+
+
+class DisplayParams(C.Structure):
+    """mrt_display_params (include/mrt.h): the presentation switches of Raytracing.h:11-12, 27-33 as parameters."""
+    _fields_ = [("tone_mapping", C.c_uint32), ("manual_srgb", C.c_uint32), ("comparison_mode", C.c_uint32),
+                ("comparison_scale", C.c_float)]
 
 
 class MrtError(RuntimeError):
@@ -101,6 +108,11 @@ SIGNATURES = {
     "mrt_event_elapsed_ms": (C.c_int, [_P, _U32, _U32, C.POINTER(C.c_float)]),
     "mrt_read_image": (C.c_int, [_P, _P]),
     "mrt_scale_image": (C.c_int, [_P, _F]),
+    "mrt_get_size": (C.c_int, [_P, C.POINTER(_U32), C.POINTER(_U32)]),
+    "mrt_display_params_default": (None, [C.POINTER(DisplayParams)]),
+    "mrt_display": (C.c_int, [_P, C.POINTER(DisplayParams), _P, _U32, _U32, _P]),
+    "mrt_checkpoint_save": (C.c_int, [_P, C.c_char_p]),
+    "mrt_checkpoint_load": (C.c_int, [_P, C.c_char_p, C.POINTER(_U32)]),
     "mrt_clear_image": (C.c_int, [_P]),
     "mrt_image_device_ptr": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_SZ)]),
     "mrt_read_buffer": (C.c_int, [_P, _U32, _P, _SZ]),

@@ -140,6 +140,38 @@ class Renderer:
         L.check(L.lib().mrt_read_image(self._ctx, L.ptr(img)))
         return img
 
+    def display(self, tone_mapping=False, manual_srgb=False, comparison_mode=L.COMPARE_DISABLED, comparison_scale=None,
+                reference=None):
+        """Presentation pass (blitFragment, Shaders.metal:33-69) of the accumulated image; reference = (RH, RW, 4)
+        float32, row 0 = bottom.  Returns (H, W, 4) float32."""
+        p = L.DisplayParams()
+        L.lib().mrt_display_params_default(C.byref(p))
+        p.tone_mapping, p.manual_srgb, p.comparison_mode = int(bool(tone_mapping)), int(bool(manual_srgb)), int(comparison_mode)
+        if comparison_scale is not None:
+            p.comparison_scale = float(comparison_scale)
+        out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        if reference is not None:
+            reference = np.ascontiguousarray(reference, dtype=np.float32)
+            rh, rw = reference.shape[:2]
+            L.check(L.lib().mrt_display(self._ctx, C.byref(p), L.ptr(reference), rw, rh, L.ptr(out)))
+        else:
+            L.check(L.lib().mrt_display(self._ctx, C.byref(p), None, 0, 0, L.ptr(out)))
+        return out
+
+    def checkpoint_save(self, path):
+        """Image + size + next frame index + accumulate mode + the three noise slots (the reference's
+        -saveCurrentImage is a stub, Renderer.mm:659-662)."""
+        L.check(L.lib().mrt_checkpoint_save(self._ctx, str(path).encode()))
+
+    def checkpoint_load(self, path):
+        """Restore a checkpoint (resizes to the stored size); returns the frame index to continue from."""
+        n = C.c_uint32()
+        L.check(L.lib().mrt_checkpoint_load(self._ctx, str(path).encode(), C.byref(n)))
+        w, h = C.c_uint32(), C.c_uint32()
+        L.check(L.lib().mrt_get_size(self._ctx, C.byref(w), C.byref(h)))
+        self.width, self.height, self.frame_index = w.value, h.value, n.value
+        return n.value
+
     def read_image_into(self, host_address):
         L.check(L.lib().mrt_read_image(self._ctx, C.c_void_p(int(host_address))))
 

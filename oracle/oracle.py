@@ -70,6 +70,7 @@ def lib():
             "orc_generateNextBounce": (None, [P, P, F, P, P, P, P]),
             "orc_lightTriangleSamplePDF": (F, [F, F, P, P, P]),
             "orc_triangle_test": (None, [P, P, F, F, P, P, P, P, P]), "orc_sizeof": (U, [U]),
+            "orc_display": (None, [P, U, U, U, U, U, F, P, U, U, P]), "orc_toSRGB": (F, [F]),
         }
         for n, (r, a) in sig.items():
             fn = getattr(h, n)
@@ -172,3 +173,19 @@ class Oracle:
         out = np.empty(n, INTERSECTION)
         lib().orc_intersect_host(self._c, _p(rays), stride, n, _p(out), int(bvh))
         return out
+
+
+def display(image, tone_mapping=False, manual_srgb=False, comparison_mode=0, comparison_scale=10.0, reference=None):
+    """Presentation pass of the reference (Shaders.metal:33-69) on an (H, W, 4) float32 image; reference = (RH, RW, 4)."""
+    image = np.ascontiguousarray(image, np.float32)
+    h, w = image.shape[:2]
+    out = np.empty_like(image)
+    if reference is not None:
+        reference = np.ascontiguousarray(reference, np.float32)
+        rh, rw = reference.shape[:2]
+        lib().orc_display(_p(image), w, h, int(tone_mapping), int(manual_srgb), int(comparison_mode), float(comparison_scale),
+                          _p(reference), rw, rh, _p(out))
+    else:
+        lib().orc_display(_p(image), w, h, int(tone_mapping), int(manual_srgb), int(comparison_mode), float(comparison_scale),
+                          None, 0, 0, _p(out))
+    return out

@@ -18,6 +18,7 @@
 #include <vector>
 #include "orc_bvh.h"
 #include "orc_kernels.h"
+#include "orc_display.h"
 
 using namespace orc;
 
@@ -252,6 +253,14 @@ void orc_triangle_test(const float* o, const float* d, float tmin, float tmax, c
     triangle_test(ld3(o), ld3(d), tmin, tmax, ld3(v0), ld3(v1), ld3(v2), 0, best);
     *hit = best.tri == 0; tuv[0] = best.t; tuv[1] = best.u; tuv[2] = best.v;
 }
+// presentation pass (Shaders.metal:33-69): tone mapping / sRGB / comparison against a reference image
+void orc_display(const float* image, uint32_t W, uint32_t H, uint32_t toneMapping, uint32_t manualSRGB, uint32_t mode, float scale,
+                 const float* ref, uint32_t RW, uint32_t RH, float* out) {
+    DisplayParams p{toneMapping, manualSRGB, mode, scale};
+    display(image, W, H, p, ref, RW, RH, out);
+}
+float orc_toSRGB(float v) { return toSRGB(v); }
+
 uint32_t orc_sizeof(uint32_t which) {
     switch (which) { case 0: return sizeof(Ray); case 1: return sizeof(LightSamplingRay); case 2: return sizeof(Intersection);
         case 3: return sizeof(Vertex); case 4: return sizeof(Material); case 5: return sizeof(TriangleReference);
