@@ -17,10 +17,12 @@ namespace mrt {
 
 #define MRT_STACK8 32          /* node groups; host checks the tree depth against it (api.cu) */
 
-template <class IO>
+template <class IO, bool COUNT = false>
 __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nodes8, const float4* __restrict__ tris,
                                                   uint32_t total, unsigned int* head, uint32_t refillBelow, uint32_t leafMin,
-                                                  uint32_t magic, IO& io) {
+                                                  uint32_t magic, IO& io, unsigned long long* visits = nullptr) {
+    // COUNT: diagnostic build that adds up node tests and triangle tests into visits[0], visits[1] (MRT_TRACE_COUNT=1)
+    uint32_t nNodes = 0, nTris = 0;
     // magic = 0x47000000 arrives as a kernel PARAMETER: were it a literal, ptxas would make it PRMT's immediate and
     // spend an extra move per plane on the byte selector instead (bvh8.h: mrt_plane)
     // visiting order of child slots per ray octant: lut[c][x] = x with bit i moved to bit i ^ c
@@ -103,6 +105,7 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
                         w[12] = __float_as_uint(q3.x); w[13] = __float_as_uint(q3.y); w[14] = __float_as_uint(q3.z); w[15] = __float_as_uint(q3.w);
                         w[16] = __float_as_uint(q4.x); w[17] = __float_as_uint(q4.y); w[18] = __float_as_uint(q4.z); w[19] = __float_as_uint(q4.w);
                     }
+                    if (COUNT) ++nNodes;
                     const uint32_t hs = bvh8_hit_slots(w, r, tmin, best.t);
                     const uint32_t imask = w[3] >> 24;
                     gx = w[4]; gy = ((hs & imask) << 24) | imask;
@@ -117,6 +120,7 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
             if (wantTri) {                                  // one triangle per step: lanes with longer lists re-vote
                 const int k = __ffs(ty) - 1;
                 ty &= ty - 1u;
+                if (COUNT) ++nTris;
                 triangle_test(tris, tx + uint32_t(k), o, d, tmin, tmax, best);
                 if (target != MRT_NO_HIT && best.tri != target) {                // any-hit job: occluded, done
                     ty = 0; io.store(tag, target, best); alive = false;
@@ -128,6 +132,10 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
             const unsigned a2 = __ballot_sync(0xffffffffu, alive);
             if (a2 == 0 || (!exhausted && __popc(a2) < (int)refillBelow)) break;
         }
+    }
+    if (COUNT && visits) {
+        nNodes = __reduce_add_sync(0xffffffffu, nNodes); nTris = __reduce_add_sync(0xffffffffu, nTris);
+        if (lane == 0) { atomicAdd(visits, (unsigned long long)nNodes); atomicAdd(visits + 1, (unsigned long long)nTris); }
     }
 }
 

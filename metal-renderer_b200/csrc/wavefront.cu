@@ -89,7 +89,7 @@ struct WfIO {
     }
 };
 
-template <int MINB, int WIDE>
+template <int MINB, int WIDE, bool COUNT = false>
 __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers b, uint32_t parity, uint32_t refillBelow,
                                                         uint32_t leafMin, uint32_t magic, unsigned long long* counters) {
     const uint32_t nExt = b.counts[2 * parity], nShadow = b.counts[2 * parity + 1];
@@ -100,7 +100,8 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     }
     WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
-    if (WIDE) trace_persistent8(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic, io);
+    if (WIDE) trace_persistent8<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic, io,
+                                             counters ? counters + 2 : nullptr);
     else trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
 }
 
@@ -357,7 +358,10 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
 #define MRT_LAUNCH_TRACE(MB, WD) k_wf_trace<MB, WD><<<blocks(MB), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters)
-    if (t.wide) {
+    static const int countVisits = env_int("MRT_TRACE_COUNT", 0);      // diagnostic: node / triangle tests into stats
+    if (t.wide && countVisits && p.counters) {
+        k_wf_trace<8, 1, true><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters);
+    } else if (t.wide) {
         if (t.minb >= 12) MRT_LAUNCH_TRACE(12, 1); else if (t.minb >= 10) MRT_LAUNCH_TRACE(10, 1);
         else if (t.minb >= 8) MRT_LAUNCH_TRACE(8, 1); else if (t.minb >= 6) MRT_LAUNCH_TRACE(6, 1); else MRT_LAUNCH_TRACE(5, 1);
     } else {
@@ -379,7 +383,10 @@ void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     // MRT_SHADE_MINBLOCKS: 4 (default) = 64 registers with a 56-byte spill frame, 3 = 80 registers; the kernel is
     // latency-bound (ncu pass O: 36 % warps active, long scoreboard), so occupancy wins: +3.6 % per step in pass P
     static const int minb = env_int("MRT_SHADE_MINBLOCKS", 4);
-    if (minb >= 4) {
+    if (minb >= 5) {
+        if (countRays) k_wf_shade<true, 5><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
+        else           k_wf_shade<false, 5><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
+    } else if (minb >= 4) {
         if (countRays) k_wf_shade<true, 4><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
         else           k_wf_shade<false, 4><<<blocks, 256, 0, s>>>(p, b, outParity, first ? 1u : 0u, wave);
     } else {

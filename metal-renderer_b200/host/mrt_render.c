@@ -103,11 +103,13 @@ int main(int argc, char** argv) {
     double samples = (double)w * h * frames;
     printf("{\"scene\": \"%s\", \"triangles\": %u, \"lights\": %u, \"width\": %u, \"height\": %u, \"frames\": %u, \"depth\": %u, "
            "\"device_ms\": %.3f, \"wall_ms\": %.3f, \"msamples_per_s\": %.2f, \"mrays_per_s\": %.2f, \"primary_rays\": %llu, "
-           "\"shadow_rays\": %llu, \"kernel_launches\": %llu, \"bvh_nodes\": %u, \"bvh_depth\": %u, \"bvh_build_ms\": %.1f}\n",
+           "\"shadow_rays\": %llu, \"kernel_launches\": %llu, \"bvh_nodes\": %u, \"bvh_depth\": %u, \"bvh_build_ms\": %.1f, "
+           "\"bvh8_nodes\": %u, \"bvh8_depth\": %u, \"node_tests\": %llu, \"triangle_tests\": %llu}\n",
            scene_name, view.triangle_count, view.light_count, w, h, frames, depth, st.last_render_ms, (t1 - t0) * 1e3,
            samples / (st.last_render_ms * 1e3), (double)(st.primary_rays + st.shadow_rays) / (st.last_render_ms * 1e3),
            (unsigned long long)st.primary_rays, (unsigned long long)st.shadow_rays, (unsigned long long)st.kernel_launches,
-           st.bvh_nodes, st.bvh_depth, st.bvh_build_ms);
+           st.bvh_nodes, st.bvh_depth, st.bvh_build_ms, st.bvh8_nodes, st.bvh8_depth,
+           (unsigned long long)st.nodes_visited, (unsigned long long)st.triangles_tested);   /* MRT_TRACE_COUNT=1 fills the last two */
     if (checkpoint) CHECK(mrt_checkpoint_save(ctx, checkpoint));
     if (out && (tone || srgb)) {
         mrt_display_params dp;
