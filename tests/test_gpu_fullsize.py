@@ -65,3 +65,38 @@ def test_4k_row_shards_compose():
         acc[g::2] = r.save_current_image()[g::2]
         r.close()
     assert bits_equal(acc, ref)
+
+
+_VARIANT_SCRIPT = r"""
+import sys
+sys.path[:0] = [%(pkg)r, %(tests)r]
+import mrt_b200 as m
+from helpers import bits_equal
+from test_gpu_fullsize import gpu_renderer
+scene = m.Scene.procedural("spheres-64k", 3)
+tiles = m.noise_tiles(5, 0, 3)
+a = gpu_renderer(scene, 1024, 576, pipeline=m.PIPELINE_WAVEFRONT)      # 589,824 slots: enough for two slot groups
+b = gpu_renderer(scene, 1024, 576, pipeline=m.PIPELINE_MEGAKERNEL)     # binary tree, one thread per pixel
+a.draw(3, tiles); b.draw(3, tiles)
+sa, sb = a.stats(), b.stats()
+assert bits_equal(a.save_current_image(), b.save_current_image()), "image differs"
+assert (sa["primary_rays"], sa["shadow_rays"]) == (sb["primary_rays"], sb["shadow_rays"]), "ray counts differ"
+print("variant ok", sa["kernel_launches"])
+"""
+
+
+@pytest.mark.parametrize("env", [
+    {"MRT_WF_SPLIT": "2"}, {"MRT_WF_SPLIT": "3"},                       # slot groups on separate streams
+    {"MRT_WF_REGION": "256"}, {"MRT_WF_REGION": "0"},                   # work-claim granularity
+    {"MRT_BVH_WIDTH": "2"},                                             # binary tree in the persistent trace kernel
+    {"MRT_TRACE_MINBLOCKS": "6", "MRT_TRACE_REFILL": "28", "MRT_TRACE_LEAFMIN": "4", "MRT_TRACE_TRIRATIO": "0"},
+    {"MRT_SHADE_MINBLOCKS": "3"}, {"MRT_TRACE_COUNT": "1"},
+], ids=lambda e: ",".join(f"{k[4:].lower()}={v}" for k, v in e.items()))
+def test_tuning_switches_do_not_change_the_bits(env):
+    """Every scheduling knob of csrc/wavefront.cu / api.cu (read once per process from the environment) must leave the
+    image and the ray counts bit-identical: the wavefront render under the knob == the megakernel render."""
+    import os, pathlib, subprocess, sys
+    root = pathlib.Path(__file__).resolve().parent.parent
+    script = _VARIANT_SCRIPT % dict(pkg=str(root / "metal-renderer_b200"), tests=str(root / "tests"))
+    out = subprocess.run([sys.executable, "-c", script], env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "variant ok" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
