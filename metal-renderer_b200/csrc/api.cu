@@ -62,6 +62,7 @@ struct mrt_ctx {
     void* dTriSlot = nullptr;                    // original triangle index -> leaf-order record
     void* dNodes8 = nullptr; void* dTris8 = nullptr;   // 8-wide tree (bvh8.h)
     WfBuffers wf{};                              // wavefront path state + queues (sized by mrt_resize)
+    uint32_t wfSlotMult = 1;                     // path slots per pixel (MRT_WF_SLOTS)
     uint32_t nextFrame = 0;                      // frame index after the last one accumulated (checkpoint)
     bool profile = getenv("MRT_WAVE_LOG") != nullptr;                        // event pair around every trace launch
     std::vector<cudaEvent_t> profEvents; size_t profUsed = 0;
@@ -285,7 +286,10 @@ int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
     CK(cudaMemsetAsync(c->dImage, 0, n * sizeof(float4), c->stream));
     c->W = width; c->H = height;
     {   // wavefront path state: one slot per pixel of an 8x4-tiled grid, SoA float4 arrays + two queue pairs
-        const size_t slots = (size_t)((width + 7u) / 8u) * ((height + 3u) / 4u) * 32u;
+        // MRT_WF_SLOTS: path slots per pixel (default 1).  More slots than pixels = fewer, larger waves.
+        static const int slotMult = std::min(4, std::max(1, getenv("MRT_WF_SLOTS") ? atoi(getenv("MRT_WF_SLOTS")) : 1));
+        c->wfSlotMult = (uint32_t)slotMult;
+        const size_t slots = (size_t)((width + 7u) / 8u) * ((height + 3u) / 4u) * 32u * slotMult;
         const size_t f4 = slots * sizeof(float4), u4 = slots * sizeof(uint32_t);
         const size_t regions = slots / 32;                                  // smallest region = one 8x4 tile
         const size_t total = 7 * f4 + 6 * u4 + 128 + 2 * regions * sizeof(uint32_t);      // 128 = 4 groups x (counts[4], heads[2], 2 spare)
@@ -457,7 +461,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             // sub-batches so that the sample buffer (16 B per sample) stays within a quarter of the free device memory.
             WfBuffers b = c->wf;
             b.pixels = ((c->W + 7u) / 8u) * ((p.ownedRows + 3u) / 4u) * 32u;
-            b.slots = b.pixels;
+            b.slots = b.pixels * c->wfSlotMult;
             const bool count = c->cfg.count_rays != 0;
             size_t freeB = 0, totalB = 0;
             CK(cudaMemGetInfo(&freeB, &totalB));

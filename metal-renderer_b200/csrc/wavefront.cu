@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(256, MINB) k_wf_shade(RenderParams P, WfBuffer
     };
     if (rs == 32u) {
         if (mW) {
-            if (lane == 0) claim((b.slotBase + slot) >> 5, (b.slotBase + slot) >> 5, __popc(mW));
+            if (lane == 0) claim((b.slotBase + slot) >> 5, ((b.slotBase + slot) >> 5) % R, __popc(mW));
             jBase = __shfl_sync(0xffffffffu, jBase, 0); jLim = __shfl_sync(0xffffffffu, jLim, 0); jCur = __shfl_sync(0xffffffffu, jCur, 0);
         }
     } else {
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(256, MINB) k_wf_shade(RenderParams P, WfBuffer
         if (threadIdx.x == 0) {
             uint32_t a = 0;
             for (int w = 0; w < 8; ++w) { uint32_t n = sW[w]; sW[w] = a; a += n; }
-            if (a) claim(blockIdx.x + b.slotBase / 256u, (uint32_t)(((unsigned long long)blockIdx.x * 256u + b.slotBase) / rs), a);
+            if (a) claim(blockIdx.x + b.slotBase / 256u, (uint32_t)((((unsigned long long)blockIdx.x * 256u + b.slotBase) / rs) % R), a);
             sBase[2] = jBase; sBase[3] = jLim; sBase[4] = jCur;
         }
         __syncthreads();
