@@ -139,4 +139,148 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
     }
 }
 
+// Variant with POSTPONED triangles (MRT_TRACE_DEFER=1): a lane that finds leaf triangles keeps descending while it has
+// inner work, parking up to MRT_TQUEUE triangle groups; the warp takes a triangle step when `triThresh` lanes hold
+// triangles (or `leafMin` lanes have nothing else left).  Triangle steps then run with more lanes and lanes holding
+// triangles no longer idle through node steps; the price is that the nearest-hit bound tightens later, so a ray may
+// test a few nodes the ordered traversal would have culled.  The answer is unchanged: it is the minimum over all
+// triangles of (t, index), whatever the order.
+#define MRT_TQUEUE 4u
+
+template <class IO, bool COUNT = false>
+__device__ __forceinline__ void trace_persistent8d(const float4* __restrict__ nodes8, const float4* __restrict__ tris,
+                                                  uint32_t total, unsigned int* head, uint32_t refillBelow, uint32_t leafMin,
+                                                  uint32_t magic, IO& io, unsigned long long* visits = nullptr) {
+    // COUNT: diagnostic build that adds up node tests and triangle tests into visits[0], visits[1] (MRT_TRACE_COUNT=1)
+    uint32_t nNodes = 0, nTris = 0;
+    // magic = 0x47000000 arrives as a kernel PARAMETER: were it a literal, ptxas would make it PRMT's immediate and
+    // spend an extra move per plane on the byte selector instead (bvh8.h: mrt_plane)
+    // visiting order of child slots per ray octant: lut[c][x] = x with bit i moved to bit i ^ c
+    __shared__ uint8_t orderLut[8 * 256];
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) orderLut[i] = (uint8_t)mrt_perm8(i & 0xffu, i >> 8);
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u;
+    const float tiny = 1e-30f;
+    // leafMin carries the vote tuning: bits 0-7 = lanes with triangles that force a triangle step, bits 8-15 = ratio r
+    // (triangle step as soon as 16 * lanes-with-triangles >= r * lanes-with-node-work; 0 = off).  A triangle step
+    // costs ~0.4 node steps, so r = 6 picks whichever step advances more lanes per instruction (pass M: +2 %; an L1
+    // prefetch of the leaf's first triangle at the end of the node step was tried there too and lost 1-20 %).
+    const int triRatio = int((leafMin >> 8) & 0xffu);
+    const int triThresh = int((leafMin >> 18) & 0x3fu) ? int((leafMin >> 18) & 0x3fu) : 16;    // bits 18-23: see below
+    leafMin &= 0xffu;
+    bool alive = false, exhausted = (total == 0);
+    uint32_t tag = 0, target = MRT_NO_HIT;
+    f3 o = mk3(0.f, 0.f, 0.f), d = o;
+    float tmin = 0.f, tmax = 0.f;
+    Ray8 r; r.ox = r.oy = r.oz = 0.f; r.invx = r.invy = r.invz = 0.f; r.negx = r.negy = r.negz = 0u; r.octInv = 0u; r.magic = magic;
+    HitRec best; best.t = 0.f; best.tri = MRT_NO_HIT; best.u = best.v = 0.f;
+    uint32_t gx = 0, gy = 0, tx = 0, ty = 0;
+    uint2 stack[MRT_STACK8];
+    int sp = 0;
+    uint2 tq[MRT_TQUEUE];                                  // postponed triangle groups, oldest (nearest) first
+    uint32_t th = 0, tn = 0;                               // queue head index, entries queued
+
+    for (;;) {
+        // ---- refill idle lanes until enough of the warp is busy (or the queue is empty) ----
+        unsigned am;
+        for (;;) {
+            am = __ballot_sync(0xffffffffu, alive);
+            if (exhausted || __popc(am) >= (int)refillBelow) break;
+            unsigned need = ~am;
+            uint32_t n = __popc(need), base = 0;
+            int leader = __ffs(need) - 1;
+            if ((int)lane == leader) base = atomicAdd(head, n);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!alive) {
+                uint32_t it = base + __popc(need & ((1u << lane) - 1u));
+                if (it < total) {
+                    TraceJob job;
+                    if (io.load(it, job)) {
+                        tag = job.tag; o = job.o; d = job.d; tmin = job.tmin; tmax = job.tmax; target = job.target;
+                        r.ox = o.x; r.oy = o.y; r.oz = o.z;
+                        r.invx = __fdiv_rn(1.0f, fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x);
+                        r.invy = __fdiv_rn(1.0f, fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y);
+                        r.invz = __fdiv_rn(1.0f, fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z);
+                        r.negx = __float_as_uint(d.x) >> 31; r.negy = __float_as_uint(d.y) >> 31; r.negz = __float_as_uint(d.z) >> 31;
+                        r.octInv = 7u - (r.negx | (r.negy << 1) | (r.negz << 2));
+                        best.t = tmax; best.tri = target; best.u = 0.0f; best.v = 0.0f;
+                        gx = 0; gy = 0x01000000u; tx = 0; ty = 0; sp = 0; th = 0; tn = 0;       // group holding just the root (as slot 0)
+                        alive = true;
+                    }
+                }
+            }
+            exhausted = base + n >= total;
+        }
+        if (am == 0) break;                               // queue empty and every lane idle
+
+        for (;;) {
+            // a lane holding triangles keeps taking node steps while it has inner work and room to postpone another
+            // group; lanes with nothing but triangles left are the ones a triangle step must not keep waiting
+            const bool wantTri = alive && ty != 0;
+            const bool wantNode = alive && (gy & 0xff000000u) != 0u && tn < MRT_TQUEUE;
+            const unsigned mN = __ballot_sync(0xffffffffu, wantNode);
+            const unsigned mT = __ballot_sync(0xffffffffu, wantTri);
+            const unsigned mO = __ballot_sync(0xffffffffu, wantTri && !wantNode);
+            if ((mN | mT) == 0) break;
+            const int nT = __popc(mT), nN = __popc(mN), nO = __popc(mO);
+            if (mN != 0 && nO < (int)leafMin && nT < triThresh && (triRatio == 0 || 16 * nO < triRatio * nN)) {
+                if (wantNode) {
+                    // nearest unvisited inner child in octant order (G keeps its hits in slot space)
+                    const uint32_t pr = orderLut[(r.octInv << 8) | (gy >> 24)];
+                    const uint32_t slot = uint32_t(31 - __clz(pr)) ^ r.octInv;
+                    gy &= ~(0x01000000u << slot);
+                    if (gy & 0xff000000u) stack[sp++] = make_uint2(gx, gy);
+                    const uint32_t rel = __popc(gy & 0xffu & ((1u << slot) - 1u));
+                    const float4* np = nodes8 + 5 * (size_t)(gx + rel);
+                    uint32_t w[20];
+                    {
+                        float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3), q4 = __ldg(np + 4);
+                        w[0] = __float_as_uint(q0.x); w[1] = __float_as_uint(q0.y); w[2] = __float_as_uint(q0.z); w[3] = __float_as_uint(q0.w);
+                        w[4] = __float_as_uint(q1.x); w[5] = __float_as_uint(q1.y); w[6] = __float_as_uint(q1.z); w[7] = __float_as_uint(q1.w);
+                        w[8] = __float_as_uint(q2.x); w[9] = __float_as_uint(q2.y); w[10] = __float_as_uint(q2.z); w[11] = __float_as_uint(q2.w);
+                        w[12] = __float_as_uint(q3.x); w[13] = __float_as_uint(q3.y); w[14] = __float_as_uint(q3.z); w[15] = __float_as_uint(q3.w);
+                        w[16] = __float_as_uint(q4.x); w[17] = __float_as_uint(q4.y); w[18] = __float_as_uint(q4.z); w[19] = __float_as_uint(q4.w);
+                    }
+                    if (COUNT) ++nNodes;
+                    const uint32_t hs = bvh8_hit_slots(w, r, tmin, best.t);
+                    const uint32_t imask = w[3] >> 24;
+                    gx = w[4]; gy = ((hs & imask) << 24) | imask;
+                    if (!(gy & 0xff000000u) && sp > 0) { uint2 e = stack[--sp]; gx = e.x; gy = e.y; }   // G always holds the next inner work
+                    const uint32_t nt = bvh8_triangle_mask(w[6], w[7], hs & ~imask);
+                    if (nt != 0u) {
+                        if (ty == 0u) { tx = w[5]; ty = nt; }
+                        else { tq[(th + tn) % MRT_TQUEUE] = make_uint2(w[5], nt); ++tn; }
+                    }
+                    if (ty == 0u && !(gy & 0xff000000u)) {                      // nothing left anywhere: done
+                        if (best.tri == MRT_NO_HIT) best.t = -1.0f;
+                        io.store(tag, target, best); alive = false;
+                    }
+                }
+                continue;
+            }
+            if (wantTri) {                                  // one triangle per step: lanes with longer lists re-vote
+                const int k = __ffs(ty) - 1;
+                ty &= ty - 1u;
+                if (COUNT) ++nTris;
+                triangle_test(tris, tx + uint32_t(k), o, d, tmin, tmax, best);
+                if (target != MRT_NO_HIT && best.tri != target) {                // any-hit job: occluded, done
+                    ty = 0; io.store(tag, target, best); alive = false;
+                } else if (ty == 0u) {
+                    if (tn != 0u) { uint2 e = tq[th]; tx = e.x; ty = e.y; th = (th + 1u) % MRT_TQUEUE; --tn; }
+                    else if (!(gy & 0xff000000u)) {
+                        if (best.tri == MRT_NO_HIT) best.t = -1.0f;
+                        io.store(tag, target, best); alive = false;
+                    }
+                }
+            }
+            const unsigned a2 = __ballot_sync(0xffffffffu, alive);
+            if (a2 == 0 || (!exhausted && __popc(a2) < (int)refillBelow)) break;
+        }
+    }
+    if (COUNT && visits) {
+        nNodes = __reduce_add_sync(0xffffffffu, nNodes); nTris = __reduce_add_sync(0xffffffffu, nTris);
+        if (lane == 0) { atomicAdd(visits, (unsigned long long)nNodes); atomicAdd(visits + 1, (unsigned long long)nTris); }
+    }
+}
+
 }  // namespace mrt

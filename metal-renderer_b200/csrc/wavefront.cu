@@ -100,7 +100,9 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     }
     WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
-    if (WIDE) trace_persistent8<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic, io,
+    if (WIDE == 2) trace_persistent8d<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic, io,
+                                                   counters ? counters + 2 : nullptr);
+    else if (WIDE) trace_persistent8<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic, io,
                                              counters ? counters + 2 : nullptr);
     else trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
 }
@@ -318,11 +320,12 @@ static int device_sms() {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     return n > 0 ? n : 148;
 }
-struct TraceTuning { int minb, refill, leafMin, wide, triRatio; };
+struct TraceTuning { int minb, refill, leafMin, wide, triRatio, defer, triThresh; };
 static TraceTuning trace_tuning() {
     static const int wide = env_int("MRT_BVH_WIDTH", 8) == 8 ? 1 : 0;
     static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", wide ? 8 : 10), env_int("MRT_TRACE_REFILL", 24),
-                                   env_int("MRT_TRACE_LEAFMIN", 8), wide, env_int("MRT_TRACE_TRIRATIO", 6) };
+                                   env_int("MRT_TRACE_LEAFMIN", 8), wide, env_int("MRT_TRACE_TRIRATIO", 6),
+                                   env_int("MRT_TRACE_DEFER", 0), env_int("MRT_TRACE_TRITHRESH", 16) };
     return t;
 }
 
@@ -336,7 +339,8 @@ void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const voi
     const uint32_t warpsNeeded = (count + 31u) / 32u;
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
     const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin)) |
-                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8);
+                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8) |
+                             ((uint32_t)(t.triThresh < 1 ? 1 : (t.triThresh > 33 ? 33 : t.triThresh)) << 18);
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); uint32_t need = (warpsNeeded + 3u) / 4u; return need < cap ? need : cap; };
 #define MRT_LAUNCH_ISECT(MB, WD) k_intersect_persistent<MB, WD><<<blocks(MB), 128, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, head, refill, leafMin, 0x47000000u)
     if (t.wide) {
@@ -353,13 +357,17 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     const TraceTuning t = trace_tuning();
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
     const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin)) |
-                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8);
+                             ((uint32_t)(t.triRatio < 0 ? 0 : (t.triRatio > 255 ? 255 : t.triRatio)) << 8) |
+                             ((uint32_t)(t.triThresh < 1 ? 1 : (t.triThresh > 33 ? 33 : t.triThresh)) << 18);
     const uint32_t parity = wave & 1u;
     const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
 #define MRT_LAUNCH_TRACE(MB, WD) k_wf_trace<MB, WD><<<blocks(MB), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters)
     static const int countVisits = env_int("MRT_TRACE_COUNT", 0);      // diagnostic: node / triangle tests into stats
-    if (t.wide && countVisits && p.counters) {
+    if (t.wide && t.defer) {                                           // postponed triangles (device_trace8.cuh)
+        if (countVisits && p.counters) k_wf_trace<8, 2, true><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters);
+        else MRT_LAUNCH_TRACE(8, 2);
+    } else if (t.wide && countVisits && p.counters) {
         k_wf_trace<8, 1, true><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters);
     } else if (t.wide) {
         if (t.minb >= 12) MRT_LAUNCH_TRACE(12, 1); else if (t.minb >= 10) MRT_LAUNCH_TRACE(10, 1);

@@ -91,6 +91,7 @@ print("variant ok", sa["kernel_launches"])
     {"MRT_BVH_WIDTH": "2"},                                             # binary tree in the persistent trace kernel
     {"MRT_TRACE_MINBLOCKS": "6", "MRT_TRACE_REFILL": "28", "MRT_TRACE_LEAFMIN": "4", "MRT_TRACE_TRIRATIO": "0"},
     {"MRT_SHADE_MINBLOCKS": "3"}, {"MRT_TRACE_COUNT": "1"},
+    {"MRT_TRACE_DEFER": "1"}, {"MRT_TRACE_DEFER": "1", "MRT_TRACE_TRITHRESH": "28", "MRT_TRACE_LEAFMIN": "16"},   # postponed triangles
     {"MRT_WF_SLOTS": "2"}, {"MRT_WF_SLOTS": "3", "MRT_WF_SPLIT": "2"},  # more path slots than pixels (fewer, larger waves)
 ], ids=lambda e: ",".join(f"{k[4:].lower()}={v}" for k, v in e.items()))
 def test_tuning_switches_do_not_change_the_bits(env):
