@@ -371,6 +371,7 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
         k_wf_trace<8, 1, true><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters);
     } else if (t.wide) {
         if (t.minb >= 12) MRT_LAUNCH_TRACE(12, 1); else if (t.minb >= 10) MRT_LAUNCH_TRACE(10, 1);
+        else if (t.minb >= 9) MRT_LAUNCH_TRACE(9, 1);
         else if (t.minb >= 8) MRT_LAUNCH_TRACE(8, 1); else if (t.minb >= 6) MRT_LAUNCH_TRACE(6, 1); else MRT_LAUNCH_TRACE(5, 1);
     } else {
         if (t.minb >= 12) MRT_LAUNCH_TRACE(12, 0); else if (t.minb >= 10) MRT_LAUNCH_TRACE(10, 0);
