@@ -8,7 +8,10 @@
 // PARITY STATUS: the reference ships no tests, golden vectors or CPU path for this pipeline, and its
 // intersector is closed source, so the END-TO-END oracle is "parity unpinned" (SURVEY.md §8c).  What is
 // pinned: struct layouts and the host-side functions of Raytracing.h against the reference header compiled
-// here (oracle/ref_probe.cpp -> tests/golden/*.json), plus analytic known-answer tests per function.
+// here (oracle/ref_probe.cpp -> tests/golden/*.json), analytic known-answer tests per function, and — statistically,
+// not bit for bit — the whole pipeline against the Mitsuba images the reference ships as its comparison targets
+// (renderer/Media/reference/*.exr -> tests/golden/mitsuba_reference.npz; tests/test_mitsuba_sanity.py: mean radiance
+// within 0.3 % at path lengths 2, 3 and 8 at Mitsuba's resolution, 2.7 % at the CPU test's 100x75).
 #include <atomic>
 #include <chrono>
 #include <cstdio>
