@@ -521,7 +521,9 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
                     b.regions = (b.pixels + b.regionSize - 1u) / b.regionSize;
                     for (uint32_t g = 0; g < groups; ++g) { gb[g].regionSize = b.regionSize; gb[g].regions = b.regions; }
                 }
-                CK(cudaMemsetAsync(b.counts, 0, 32 * sizeof(unsigned int), c->stream));    // per group: counts[4], heads[2]
+                // per group: counts[4], heads[2]; word 7 of group 0 is the sticky failure flag (check_drained) and stays
+                CK(cudaMemsetAsync(b.counts, 0, 7 * sizeof(unsigned int), c->stream));
+                CK(cudaMemsetAsync(b.counts + 8, 0, 24 * sizeof(unsigned int), c->stream));
                 CK(cudaMemsetAsync(b.regionNext, 0, (size_t)b.regions * sizeof(unsigned int), c->stream));
                 const bool forked = stream_of(0) != c->stream;
                 if (forked) {
@@ -569,11 +571,22 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
     return MRT_OK;
 }
 
+// Failure detection of the wavefront schedule: k_wf_resolve_samples leaves a non-zero word when a batch ended with rays
+// still queued or work items unclaimed (the wave bound of mrt_render_frames would have to be wrong).  Every call that
+// hands results to the caller checks it after its stream synchronisation, so a short render can never pass silently.
+static int check_drained(mrt_ctx* c) {
+    if (!c->wf.counts) return MRT_OK;
+    unsigned int undrained = 0;
+    CK(cudaMemcpy(&undrained, c->wf.counts + 7, sizeof undrained, cudaMemcpyDeviceToHost));
+    NEED(undrained == 0, MRT_E_STATE, "wavefront batch ended with %u rays still queued (wave bound too small)", undrained);
+    return MRT_OK;
+}
+
 int mrt_sync(mrt_ctx* c) {
     NEED(c, MRT_E_INVALID, "ctx is NULL");
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaStreamSynchronize(c->stream));
-    return MRT_OK;
+    return check_drained(c);
 }
 
 int mrt_event_record(mrt_ctx* c, uint32_t slot) {
@@ -596,7 +609,7 @@ int mrt_read_image(mrt_ctx* c, float* rgba) {
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaMemcpyAsync(rgba, c->dImage, (size_t)c->W * c->H * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
-    return MRT_OK;
+    return check_drained(c);
 }
 int mrt_scale_image(mrt_ctx* c, float scale) {
     NEED(c && c->dImage, MRT_E_STATE, "no image");
@@ -736,11 +749,7 @@ int mrt_get_stats(mrt_ctx* c, mrt_stats* out) {
     CK(cudaStreamSynchronize(c->stream));
     unsigned long long h[4];
     CK(cudaMemcpy(h, c->dCounters, sizeof h, cudaMemcpyDeviceToHost));
-    if (c->wf.counts) {
-        unsigned int undrained = 0;
-        CK(cudaMemcpy(&undrained, c->wf.counts + 7, sizeof undrained, cudaMemcpyDeviceToHost));
-        NEED(undrained == 0, MRT_E_STATE, "wavefront batch ended with %u rays still queued (wave bound too small)", undrained);
-    }
+    { int rc = check_drained(c); if (rc != MRT_OK) return rc; }
     c->stats.primary_rays = h[0]; c->stats.shadow_rays = h[1]; c->stats.nodes_visited = h[2]; c->stats.triangles_tested = h[3];
     if (c->timed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->ev0, c->ev1)); c->stats.last_render_ms = ms; }
     if (c->kernelTimed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->evK0, c->evK1)); c->stats.last_kernel_ms = ms; }
