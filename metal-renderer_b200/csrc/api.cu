@@ -479,7 +479,12 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             // waves per sub-batch of nf frames: greedy assignment finishes within (total segments / slots) + L waves, plus
             // one wave per padding pixel a slot may draw; waves that find both queues empty return at once
             const uint32_t Lp = c->cfg.max_path_length;
-            auto waves_for = [Lp](uint32_t nf) { return (uint64_t)nf * Lp + Lp + 2; };
+            // MRT_WF_MAX_WAVES (tests only): cut the schedule short to exercise the failure flag of check_drained
+            static const long long waveCap = getenv("MRT_WF_MAX_WAVES") ? atoll(getenv("MRT_WF_MAX_WAVES")) : 0;
+            auto waves_for = [Lp](uint32_t nf) {
+                const uint64_t bound = (uint64_t)nf * Lp + Lp + 2;
+                return waveCap > 0 ? std::min<uint64_t>(bound, (uint64_t)waveCap) : bound;
+            };
             uint64_t wavesTotal = 0;
             for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) wavesTotal += 4 * waves_for(std::min(maxSub, n_frames - f0));   // x4: up to 4 slot groups
             if (c->profile) {

@@ -102,3 +102,25 @@ def test_tuning_switches_do_not_change_the_bits(env):
     script = _VARIANT_SCRIPT % dict(pkg=str(root / "metal-renderer_b200"), tests=str(root / "tests"))
     out = subprocess.run([sys.executable, "-c", script], env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "variant ok" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_a_short_schedule_is_reported_not_returned():
+    """Failure detection: if the wavefront schedule ends with rays still queued (here forced with MRT_WF_MAX_WAVES), the
+    next call that hands results to the caller fails with MRT_E_STATE instead of returning a partial image."""
+    import os, pathlib, subprocess, sys
+    root = pathlib.Path(__file__).resolve().parent.parent
+    script = r"""
+import sys
+sys.path[:0] = [%r, %r]
+import mrt_b200 as m
+from test_gpu_fullsize import gpu_renderer
+r = gpu_renderer(m.Scene.procedural("cornell", 0), 128, 96, pipeline=m.PIPELINE_WAVEFRONT)
+try:
+    r.draw(4, m.noise_tiles(1, 0, 4))
+    r.save_current_image()
+    print("no error")
+except m.MrtError as e:
+    print("error", e.code)
+""" % (str(root / "metal-renderer_b200"), str(root / "tests"))
+    out = subprocess.run([sys.executable, "-c", script], env=dict(os.environ, MRT_WF_MAX_WAVES="3"), capture_output=True, text=True, timeout=300)
+    assert "error -5" in out.stdout, out.stdout[-1000:] + out.stderr[-1000:]
