@@ -238,7 +238,22 @@ int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count,
     CK(upload(&c->dShade, shade.data(), shade.size() * 4));
     CK(upload(&c->dMats, mats.data(), mats.size() * 4));
     CK(upload(&c->dLights, lts.data(), lts.size() * 4));
-    CK(upload(&c->dCdf, cdf.data(), cdf.size() * 4));
+    // guide table for selectLightTriangle (device_shading.cuh): the exact host search at the start of every slice
+    uint32_t buckets = 0;
+    std::vector<uint32_t> guide;
+    if (light_count >= 32) {
+        buckets = 64; while (buckets < 4u * light_count && buckets < 16384u) buckets <<= 1;
+        guide.resize(buckets + 1);
+        auto select = [&](float xi) { uint32_t i = 0; for (; i < light_count && cdf[i + 1] <= xi; ++i) {} return i; };   // KernelHelpers.h:49-54
+        for (uint32_t b = 0; b < buckets; ++b) guide[b] = select(float(b) / float(buckets));
+        guide[buckets] = light_count;
+    }
+    std::vector<uint32_t> cdfAndGuide(cdf.size() + guide.size());
+    std::memcpy(cdfAndGuide.data(), cdf.data(), cdf.size() * 4);
+    if (!guide.empty()) std::memcpy(cdfAndGuide.data() + cdf.size(), guide.data(), guide.size() * 4);
+    CK(upload(&c->dCdf, cdfAndGuide.data(), cdfAndGuide.size() * 4));
+    c->S.lightGuide = buckets ? reinterpret_cast<const uint32_t*>(c->dCdf) + cdf.size() : nullptr;
+    c->S.lightGuideBuckets = buckets;
     Bvh8Result bvh8;
     build_bvh8(vertices, indices, triangle_count, c->cfg.bvh_threads, bvh8);
     NEED(bvh8.depth + 2 < 32, MRT_E_INVALID, "wide BVH depth %u exceeds traversal stack", bvh8.depth);

@@ -21,6 +21,8 @@ struct DeviceScene {
     const float4* materials;    // 2 per material: diffuse.rgb emissive.r | emissive.gb ior type
     const float4* lights;       // 6 per light triangle (count + 1 sentinel)
     const float* lightCdf;      // count + 1
+    const uint32_t* lightGuide; // guide[b] = index selected at xi = b / buckets, b = 0..buckets (guide[buckets] = count); or null
+    uint32_t lightGuideBuckets; // power of two, 0 = no table (few lights)
     uint32_t lightCount;
     uint32_t triangleCount;
 };
@@ -131,8 +133,17 @@ __device__ __forceinline__ Vtx interpolate_uv(const Vtx& t0, const Vtx& t1, cons
 }
 // :49-54 — the reference scans the exclusive CDF linearly; a binary search over the same predicate
 // (cdf[index+1] <= xi) returns the same index, including the zero-area sentinel when xi >= sum(pdf).
-__device__ __forceinline__ uint32_t selectLightTriangle(float xi, const float* cdf, uint32_t trianglesCount) {
+// With many lights (config 5: 2048) the 11 dependent loads of that search were the longest chain of the shade kernel,
+// so the host also stores, for `buckets` equal slices of [0,1), the index selected at the start of each slice: the index
+// for xi lies between the entries of its slice and the next (the predicate is monotone in xi), and the search starts
+// from those bounds — same predicate, same answer, 0-2 steps.
+__device__ __forceinline__ uint32_t selectLightTriangle(float xi, const float* cdf, uint32_t trianglesCount,
+                                                        const uint32_t* guide = nullptr, uint32_t buckets = 0) {
     uint32_t lo = 0, hi = trianglesCount;
+    if (buckets != 0u && xi >= 0.0f && xi < 1.0f) {
+        const uint32_t b = min(uint32_t(xi * float(buckets)), buckets - 1u);
+        lo = __ldg(guide + b); hi = __ldg(guide + b + 1u);
+    }
     while (lo < hi) {
         uint32_t mid = (lo + hi) >> 1;
         if (__ldg(cdf + mid + 1) <= xi) lo = mid + 1; else hi = mid;
@@ -252,7 +263,7 @@ __device__ __forceinline__ bool intersection_handler(const DeviceScene& S, const
     neeBranch = bounce + 1 < maxPathLength;
 
     if (neeBranch) {                                                                            // :150-176
-        Light sel = load_light(S, selectLightTriangle(noiseSample.z, S.lightCdf, S.lightCount));
+        Light sel = load_light(S, selectLightTriangle(noiseSample.z, S.lightCdf, S.lightCount, S.lightGuide, S.lightGuideBuckets));
         Vtx lightVertex = interpolate(sel.v1, sel.v2, sel.v3, barycentric(noiseSample.w, noiseSample.x));
         f3 directionToLight;
         float lightPdf = lightTriangleSamplePDF(sel.pdf, sel.area, hitVertex.v, lightVertex, directionToLight);
