@@ -254,7 +254,11 @@ namespace {
 
 constexpr float kCostNode = 1.0f;
 // cost of one triangle test relative to one node test (8 boxes); MRT_BVH8_CPRIM overrides it for A/B sweeps
-static const float kCostPrim = getenv("MRT_BVH8_CPRIM") ? (float)atof(getenv("MRT_BVH8_CPRIM")) : 0.3f;
+// Measured (pass U, profiles/r1_u_sweep_leaf_cost.log): with vote scheduling a triangle test runs with ~8 of 32 lanes and a
+// node test with ~22, so per useful lane a triangle test costs MORE than a node test; cost 1.0 on a front split down to
+// single triangles gives 4.3 triangle + 13.0 node tests per ray instead of 6.3 + 12.1 and +4.5 % rays/s (0.3 was the
+// instruction-count ratio).
+static const float kCostPrim = getenv("MRT_BVH8_CPRIM") ? (float)atof(getenv("MRT_BVH8_CPRIM")) : 1.0f;
 constexpr uint32_t kMaxLeaf8 = 3;
 
 struct Collapse {
@@ -328,7 +332,10 @@ void build_bvh8(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n,
     auto t0 = std::chrono::steady_clock::now();
     out = Bvh8Result();
     Front front;
-    build_front(vertices, indices, n, kMaxLeaf8, threads, front);
+    // The binary front is split down to single triangles (MRT_BVH8_FRONTLEAF=1, default), so that the collapse below is
+    // free to choose every leaf size from 1 to kMaxLeaf8 itself; 3 = stop at the binary builder's own SAH leaf rule.
+    static const uint32_t frontLeaf = getenv("MRT_BVH8_FRONTLEAF") ? (uint32_t)std::min(3, std::max(1, atoi(getenv("MRT_BVH8_FRONTLEAF")))) : 1u;
+    build_front(vertices, indices, n, frontLeaf, threads, front);
     const Builder& b = front.b;
     const float pad = front.pad;
     auto finish = [&] { out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
