@@ -191,3 +191,27 @@ def test_empty_and_single_triangle_scene():
     assert_bits(r.intersect_host(rays), o.intersect_host(rays, bvh=False), "one triangle")
     r.draw(2, m.noise_tiles(1, 0, 2)); o.draw(2, m.noise_tiles(1, 0, 2))
     assert_bits(r.save_current_image(), o.save_current_image(), "one triangle image")
+
+
+def test_rays_starting_on_shared_edges_and_vertices():
+    """Hits at t = +0 / -0 on two coplanar triangles at once (origin on their shared edge, or on a vertex shared by many):
+    the tie goes to the lowest triangle index, and the nearest-hit bound becoming a signed zero must not cull the other
+    candidate (the device node test works on the sign of tf - tn, csrc/bvh8.h)."""
+    for name in ("cornell", "spheres-64k"):
+        scene = m.Scene.procedural(name, 3)
+        r, o = setup_pair(scene, 8, 8)
+        idx = scene.indices.reshape(-1, 3)[:400]
+        v = scene.vertices["v"]
+        origins = np.concatenate([v[idx[:, 0]], 0.5 * (v[idx[:, 0]] + v[idx[:, 1]]), 0.5 * (v[idx[:, 1]] + v[idx[:, 2]]),
+                                  (v[idx[:, 0]] + v[idx[:, 1]] + v[idx[:, 2]]) / np.float32(3)]).astype(np.float32)
+        dirs = np.array([[0, -1, 0], [0, 1, 0], [1, 0, 0], [-1, 0, 0], [0, 0, 1], [0, 0, -1], [0.6, -0.8, 0], [0, 0.6, 0.8],
+                         [-0.57735, 0.57735, -0.57735]], np.float32)
+        rays = random_rays(len(origins) * len(dirs), 1)
+        rays["origin"] = np.repeat(origins, len(dirs), axis=0)
+        rays["direction"] = np.tile(dirs, (len(origins), 1))
+        rays["maxDistance"][::7] = -0.0                      # a signed-zero range is a live ray (not < 0)
+        rays["maxDistance"][3::11] = 0.0
+        got = r.intersect_host(rays)
+        want = o.intersect_host(rays, bvh=(name != "cornell"))
+        assert_bits(got, want, name)
+        assert (want["distance"] == 0).sum() > 50            # the case is actually exercised
