@@ -513,7 +513,8 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             // Slot groups (experiment, MRT_WF_SPLIT=2..4; default 1 = off): the slots are cut into equal parts, each with its
             // own queues and stream, so that one group's kernels could fill the SMs freed while another group's persistent
             // trace kernel drains.  Measured on B200 (profiles/r1_k_sweep.log): 2 groups = no change, 3-4 groups 4-8 %
-            // slower — the drain tail is not what limits a wave — so the production path runs one group on one stream.
+            // slower; with the 64-register shade kernel 2 groups gain 1-2.6 %.  The production path runs
+            // one group on one stream, which keeps the per-launch event timing of the trace kernel exact.
             static const int splitEnv = getenv("MRT_WF_SPLIT") ? atoi(getenv("MRT_WF_SPLIT")) : 1;
             uint32_t groups = (uint32_t)std::min(4, std::max(1, splitEnv));
             while (groups > 1 && b.slots / groups < 262144u) --groups;                     // small images: not worth splitting
