@@ -42,9 +42,9 @@ DEFAULT_WORKLOAD = "spheres-1m-1080p"
 BYTES_PER_SEGMENT = 376      # 48 intersect + 224 shade + 48 shadow intersect + 56 resolve
 BYTES_PER_SAMPLE = 140       # raygen 16+80, accumulate 12+16+16
 BYTES_PER_RAY_TRACE = 48     # one intersect: 32 B of ray read + 16 B Intersection written
-# from profiles/r1_v_wf_trace_steady_ncu_summary.txt (ncu --set full of one steady-state k_wf_trace launch — every slot
+# from profiles/r1_x_wf_trace_steady_ncu_summary.txt (ncu --set full of one steady-state k_wf_trace launch — every slot
 # busy, mixed bounce depths — 1M triangles, 1080p)
-NCU_TRACE_DRAM_BYTES_PER_LAUNCH = 464_026_112       # 417.17 MB read + 46.85 MB written
+NCU_TRACE_DRAM_BYTES_PER_LAUNCH = 465_602_816       # 416.85 MB read + 48.75 MB written
 NCU_TRACE_ISSUE_ACTIVE = 0.695
 
 
@@ -328,7 +328,7 @@ def run_ours(args, wl):
                          "step_achieved_gbs": alg_bytes_step / (dev_ms / args.steps * 1e-3) / 1e9,
                          "issue_slot_utilisation_ncu": NCU_TRACE_ISSUE_ACTIVE,
                          "note": "BVH traversal is not a streaming kernel: ncu shows it bound by instruction issue on the ALU pipe "
-                                 "(issue slots 70 % busy, ALU pipe 65 %, DRAM < 5 %, 19 of 32 lanes active), so the HBM fraction is small by construction; "
+                                 "(issue slots 69 % busy, ALU pipe 61 %, DRAM < 5 %, 19 of 32 lanes active), so the HBM fraction is small by construction; "
                                  "traffic = dram bytes of one full-size launch from profiles/ (ncu --set full); algorithmic bytes = "
                                  "48 B per ray traced (32 B ray + 16 B Intersection, SURVEY 8d)"},
             "bvh": {"nodes": st["bvh_nodes"], "depth": st["bvh_depth"], "sah_cost": st["bvh_sah_cost"], "build_ms": st["bvh_build_ms"]},
