@@ -76,3 +76,12 @@ def test_cuda_render_agrees_with_the_references_mitsuba_images(name, depth):
     assert GPU_MEAN[0] < ratio < GPU_MEAN[1], (ratio, per_channel)
     assert (np.abs(per_channel - ratio) < 0.003).all(), per_channel
     assert rel_l1 < 0.025, rel_l1                                          # 64 pixels x 256 spp per bin vs Mitsuba's 32 spp
+    # the reference's own workflow, headless: its comparison mode (COMPARE_ABSOLUTE_VALUE, scale 10; Shaders.metal:53-55)
+    # held against the Mitsuba image — mrt_display reads the 100x75 fixture at its nearest texel
+    ref = np.concatenate([z[f"{name}-{depth}/image"], np.ones((75, 100, 1), np.float32)], axis=-1)
+    diff = r.display(comparison_mode=m.COMPARE_ABSOLUTE_VALUE, reference=ref)
+    valid = np.repeat(np.repeat(z[f"{name}-{depth}/valid"], 8, axis=0), 8, axis=1)
+    img = r.save_current_image()
+    assert np.array_equal(diff[..., 3], np.zeros_like(diff[..., 3]))        # |1 - 1| * 10
+    dark = valid & (img[..., :3].max(-1) < 1.0)                            # leave the light source itself out
+    assert diff[..., :3][dark].mean() < 0.10 * 10 * img[..., :3][dark].mean() + 0.02, diff[..., :3][dark].mean()
