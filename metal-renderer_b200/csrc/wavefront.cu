@@ -278,12 +278,19 @@ __global__ void __launch_bounds__(256, MINB) k_wf_shade(RenderParams P, WfBuffer
     const uint32_t nLive = COUNT ? __reduce_add_sync(0xffffffffu, liveShadow) : 0u;
     if (lane == 0) { sE[warp] = __popc(mE); sS[warp] = __popc(mS); sN[warp] = nLive; }
     __syncthreads();
+    // three warps each take one counter, so that the block waits for ONE global atomic round trip instead of two or three
     if (threadIdx.x == 0) {
-        uint32_t aE = 0, aS = 0, aN = 0;
-        for (int w = 0; w < 8; ++w) { uint32_t e = sE[w], s = sS[w]; sE[w] = aE; sS[w] = aS; aE += e; aS += s; aN += sN[w]; }
+        uint32_t aE = 0;
+        for (int w = 0; w < 8; ++w) { uint32_t e = sE[w]; sE[w] = aE; aE += e; }
         sBase[0] = aE ? atomicAdd(b.counts + 2 * outParity, aE) : 0u;
+    } else if (threadIdx.x == 32) {
+        uint32_t aS = 0;
+        for (int w = 0; w < 8; ++w) { uint32_t q = sS[w]; sS[w] = aS; aS += q; }
         sBase[1] = aS ? atomicAdd(b.counts + 2 * outParity + 1, aS) : 0u;
-        if (COUNT && aN) atomicAdd(P.counters + 1, (unsigned long long)aN);           // live light-sampling rays
+    } else if (COUNT && threadIdx.x == 64) {
+        uint32_t aN = 0;
+        for (int w = 0; w < 8; ++w) aN += sN[w];
+        if (aN) atomicAdd(P.counters + 1, (unsigned long long)aN);                     // live light-sampling rays
     }
     __syncthreads();
     if (pushE) b.queueExt[outParity][sBase[0] + sE[warp] + __popc(mE & lt)] = slot;
