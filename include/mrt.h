@@ -83,8 +83,8 @@ typedef struct mrt_stats {
     uint64_t shadow_rays;       /* live light-sampling rays traversed */
     uint64_t kernel_launches;   /* kernels of this library launched since mrt_create */
     uint64_t frames_rendered;
-    uint64_t nodes_visited;     /* filled only by mrt_profile_traversal */
-    uint64_t triangles_tested;  /* filled only by mrt_profile_traversal */
+    uint64_t nodes_visited;     /* filled by mrt_profile_traversal and by renders under MRT_PROFILE_VISITS */
+    uint64_t triangles_tested;  /* likewise */
     float    last_render_ms;    /* device time of the last mrt_render_frames (CUDA events) */
     uint32_t bvh_nodes;
     uint32_t bvh_depth;
@@ -144,9 +144,14 @@ int mrt_set_noise(mrt_ctx* ctx, uint32_t slot, const float* tile);
 int mrt_set_row_shard(mrt_ctx* ctx, uint32_t first_row, uint32_t row_stride);
 int mrt_set_accumulate_mode(mrt_ctx* ctx, uint32_t mode);
 int mrt_set_pipeline(mrt_ctx* ctx, uint32_t pipeline);
-/* 1: bracket every trace-kernel launch of mrt_render_frames (wavefront pipeline) with a CUDA event pair on the ctx stream,
- * so that mrt_get_stats can report the dominant kernel's own device time (costs two event records per wave). */
-int mrt_set_profile(mrt_ctx* ctx, uint32_t on);
+/* Profiling flags (OR them).  MRT_PROFILE_TRACE_TIME: bracket every trace-kernel launch of mrt_render_frames (wavefront
+ * pipeline) with a CUDA event pair on the ctx stream, so that mrt_get_stats can report the dominant kernel's own device
+ * time (costs two event records per wave).  MRT_PROFILE_VISITS: run the counting variant of the trace kernel, which adds
+ * the node tests and triangle tests of every ray into mrt_stats.nodes_visited / triangles_tested (needs count_rays;
+ * slower — for the BVH term of the roofline, never inside a timed region).  Same bits in the image either way. */
+#define MRT_PROFILE_TRACE_TIME 1u
+#define MRT_PROFILE_VISITS     2u
+int mrt_set_profile(mrt_ctx* ctx, uint32_t flags);
 
 /* ---- the six dispatch kinds, one entry point each (asynchronous on the ctx stream) ---------- */
 /* rayGenerator, Shaders.metal:75-103; bindings Renderer.mm:508-510 (noise slot frame%3). */

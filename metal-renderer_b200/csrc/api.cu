@@ -65,6 +65,7 @@ struct mrt_ctx {
     uint32_t wfSlotMult = 1;                     // path slots per pixel (MRT_WF_SLOTS)
     uint32_t nextFrame = 0;                      // frame index after the last one accumulated (checkpoint)
     bool profile = getenv("MRT_WAVE_LOG") != nullptr;                        // event pair around every trace launch
+    bool countVisits = getenv("MRT_TRACE_COUNT") && atoi(getenv("MRT_TRACE_COUNT")) != 0;   // node / triangle tests into stats
     std::vector<cudaEvent_t> profEvents; size_t profUsed = 0;
     unsigned int* dWaveCounts = nullptr; size_t waveCountCap = 0;   // per-wave queue sizes (profile mode)
     float4* dSamples = nullptr; size_t sampleCap = 0;            // per-sample radiance of a wavefront batch
@@ -351,7 +352,8 @@ int mrt_set_accumulate_mode(mrt_ctx* c, uint32_t mode) {
 }
 int mrt_set_profile(mrt_ctx* c, uint32_t on) {
     NEED(c, MRT_E_INVALID, "ctx is NULL");
-    c->profile = on != 0;
+    c->profile = (on & MRT_PROFILE_TRACE_TIME) != 0;
+    c->countVisits = (on & MRT_PROFILE_VISITS) != 0;
     return MRT_OK;
 }
 int mrt_set_pipeline(mrt_ctx* c, uint32_t pipeline) {
@@ -561,7 +563,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
                             CK(cudaMemcpyAsync(c->dWaveCounts + 2 * pw, gb[g].counts + 2 * (w & 1u), 2 * sizeof(unsigned int), cudaMemcpyDeviceToDevice, st));
                             CK(cudaEventRecord(c->profEvents[2 * pw], st));
                         }
-                        launch_wf_trace(st, q, gb[g], (uint32_t)(w & 1u));
+                        launch_wf_trace(st, q, gb[g], (uint32_t)(w & 1u), c->countVisits);
                         if (c->profile) CK(cudaEventRecord(c->profEvents[2 * pw + 1], st));
                         launch_wf_shade(st, q, gb[g], (uint32_t)w, false, count);
                     }

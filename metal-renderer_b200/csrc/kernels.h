@@ -76,7 +76,7 @@ struct WfBuffers {
     const unsigned int* allCounts; uint32_t groups;   // every group's counts block (8 words each), for the drain check
 };
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays);
-void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave);
+void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool countVisits);
 void launch_wf_resolve_samples(cudaStream_t s, const RenderParams& p, const WfBuffers& b);
 bool trace_uses_wide_bvh();   // MRT_BVH_WIDTH=2 selects the binary tree (A/B runs); default 8
 int wf_kernel_info(int* traceRegs, int* traceBlocksPerSM, int* shadeRegs);

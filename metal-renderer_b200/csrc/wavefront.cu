@@ -360,7 +360,7 @@ void launch_intersect_persistent(cudaStream_t s, const DeviceScene& S, const voi
 #undef MRT_LAUNCH_ISECT
 }
 
-void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave) {
+void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool countVisits) {
     const TraceTuning t = trace_tuning();
     const uint32_t refill = (uint32_t)(t.refill < 1 ? 1 : (t.refill > 32 ? 32 : t.refill));
     const uint32_t leafMin = (uint32_t)(t.leafMin < 1 ? 1 : (t.leafMin > 32 ? 32 : t.leafMin)) |
@@ -370,7 +370,7 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     const uint32_t maxUseful = (2u * b.slots / 32u + 3u) / 4u;                // both queues full
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
 #define MRT_LAUNCH_TRACE(MB, WD) k_wf_trace<MB, WD><<<blocks(MB), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters)
-    static const int countVisits = env_int("MRT_TRACE_COUNT", 0);      // diagnostic: node / triangle tests into stats
+    // countVisits (mrt_set_profile bit 1 / MRT_TRACE_COUNT=1): diagnostic variant adding node / triangle tests into stats
     if (t.wide && t.defer) {                                           // postponed triangles (device_trace8.cuh)
         if (countVisits && p.counters) k_wf_trace<8, 2, true><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters);
         else MRT_LAUNCH_TRACE(8, 2);

@@ -78,8 +78,9 @@ class Renderer:
     def set_accumulate_mode(self, mode):
         L.check(L.lib().mrt_set_accumulate_mode(self._ctx, mode))
 
-    def set_profile(self, on):
-        L.check(L.lib().mrt_set_profile(self._ctx, int(on)))
+    def set_profile(self, flags):
+        """flags: OR of PROFILE_TRACE_TIME (event pair per trace launch) and PROFILE_VISITS (node / triangle test counters)."""
+        L.check(L.lib().mrt_set_profile(self._ctx, int(flags)))
 
     def set_pipeline(self, pipeline):
         L.check(L.lib().mrt_set_pipeline(self._ctx, pipeline))

@@ -215,3 +215,26 @@ def test_rays_starting_on_shared_edges_and_vertices():
         want = o.intersect_host(rays, bvh=(name != "cornell"))
         assert_bits(got, want, name)
         assert (want["distance"] == 0).sum() > 50            # the case is actually exercised
+
+
+@pytest.mark.gpu
+def test_visit_counters_leave_the_image_alone():
+    """mrt_set_profile(MRT_PROFILE_VISITS): the counting variant of the trace kernel (the BVH term of bench.py's roofline)
+    renders the same bits and reports node / triangle tests; without the flag the counters stay at zero."""
+    scene = m.Scene.procedural("spheres-64k", 5)
+    tiles = m.noise_tiles(6, 2, 4)
+    plain, o = setup_pair(scene, 120, 72, max_path_length=6)
+    plain.draw(4, tiles); o.draw(4, tiles)
+    assert bits_equal(plain.save_current_image(), o.save_current_image())
+    s0 = plain.stats()
+    assert s0["nodes_visited"] == 0 and s0["triangles_tested"] == 0
+    counted, _ = setup_pair(scene, 120, 72, max_path_length=6)
+    counted.set_profile(m.PROFILE_VISITS | m.PROFILE_TRACE_TIME)
+    counted.draw(4, tiles)
+    assert bits_equal(counted.save_current_image(), plain.save_current_image())
+    s1 = counted.stats()
+    rays = s1["primary_rays"] + s1["shadow_rays"]
+    assert rays == s0["primary_rays"] + s0["shadow_rays"]
+    assert s1["nodes_visited"] >= rays                       # every traced ray tests at least the root
+    assert 0 < s1["triangles_tested"] < 64 * rays
+    assert s1["profile_trace_launches"] > 0
