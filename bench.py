@@ -262,7 +262,8 @@ def run_ours(args, wl):
         step(dev_tiles.data_ptr(), False)
     barrier()
     r.reset_stats()
-    r.set_profile(m.PROFILE_TRACE_TIME)      # CUDA-event pair around every trace-kernel launch (the dominant kernel) on the ctx stream
+    if not args.no_trace_events:
+        r.set_profile(m.PROFILE_TRACE_TIME)  # CUDA-event pair around every trace-kernel launch (the dominant kernel) on the ctx stream
 
     # ---- timed: inputs resident in HBM, CUDA events on the launching stream --------------------------------------
     with ClockSampler(dev) as clocks:
@@ -379,6 +380,8 @@ def main():
     ap.add_argument("--frames", type=int, default=0, help="override frames per step per GPU")
     ap.add_argument("--ref-frames", type=int, default=1, help="frames per step of the CPU reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-trace-events", action="store_true",
+                    help="diagnostic: timed region without the per-launch event pairs (the roofline object is then meaningless)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.frames:

@@ -477,6 +477,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             // go to a per-sample buffer and are folded into the image in frame order at the end.  The batch is cut into
             // sub-batches so that the sample buffer (16 B per sample) stays within a quarter of the free device memory.
             WfBuffers b = c->wf;
+            b.waveLog = nullptr;
             b.pixels = ((c->W + 7u) / 8u) * ((p.ownedRows + 3u) / 4u) * 32u;
             b.slots = b.pixels * c->wfSlotMult;
             const bool count = c->cfg.count_rays != 0;
@@ -558,9 +559,9 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
                 for (uint64_t w = 0; w < waves; ++w) {
                     for (uint32_t g = 0; g < groups; ++g, ++pw) {
                         cudaStream_t st = stream_of(g);
+                        gb[g].waveLog = nullptr;
                         if (c->profile) {
-                            // queue sizes of this wave (the trace kernel clears the other pair, so copy them out first)
-                            CK(cudaMemcpyAsync(c->dWaveCounts + 2 * pw, gb[g].counts + 2 * (w & 1u), 2 * sizeof(unsigned int), cudaMemcpyDeviceToDevice, st));
+                            gb[g].waveLog = c->dWaveCounts + 2 * pw;        // the trace kernel notes its queue sizes there
                             CK(cudaEventRecord(c->profEvents[2 * pw], st));
                         }
                         launch_wf_trace(st, q, gb[g], (uint32_t)(w & 1u), c->countVisits);

@@ -74,6 +74,7 @@ struct WfBuffers {
     uint32_t slots;          // path slots of this group (pointers above are already offset to the group's first slot)
     uint32_t slotBase;       // first slot of the group in the whole slot array (multiple of 256)
     const unsigned int* allCounts; uint32_t groups;   // every group's counts block (8 words each), for the drain check
+    unsigned int* waveLog;                            // profile mode: where THIS trace launch notes its two queue sizes (else null)
 };
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays);
 void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool countVisits);

@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
         // the other queue pair was consumed by the previous wave's trace; clear it for the shade that follows us
         b.counts[2 * (parity ^ 1u)] = 0; b.counts[2 * (parity ^ 1u) + 1] = 0; b.heads[parity ^ 1u] = 0;
         if (counters && nExt) atomicAdd(counters, (unsigned long long)nExt);        // live extension rays traversed
+        if (b.waveLog) { b.waveLog[0] = nExt; b.waveLog[1] = nShadow; }             // mrt_set_profile: per-wave queue sizes
     }
     WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
