@@ -289,6 +289,7 @@ def run_ours(args, wl):
     r.set_profile(0)
 
     # ---- e2e: host buffers, H2D of the noise tiles and D2H of the image inside every step ------------------------
+    step(host_tiles.data_ptr(), True)        # untimed: first use of the H2D / D2H path (the W warm-up steps above ran resident)
     barrier()
     r.reset_stats()
     t0 = time.perf_counter()
