@@ -259,7 +259,8 @@ constexpr float kCostNode = 1.0f;
 // single triangles gives 4.3 triangle + 13.0 node tests per ray instead of 6.3 + 12.1 and +4.5 % rays/s (0.3 was the
 // instruction-count ratio).
 static const float kCostPrim = getenv("MRT_BVH8_CPRIM") ? (float)atof(getenv("MRT_BVH8_CPRIM")) : 1.0f;
-constexpr uint32_t kMaxLeaf8 = 3;
+// largest leaf the collapse may form (meta byte: 3-bit unary count); MRT_BVH8_MAXLEAF=1 forces single-triangle leaves
+static const uint32_t kMaxLeaf8 = getenv("MRT_BVH8_MAXLEAF") ? (uint32_t)std::min(3, std::max(1, atoi(getenv("MRT_BVH8_MAXLEAF")))) : 3u;
 
 struct Collapse {
     const Builder& b;
