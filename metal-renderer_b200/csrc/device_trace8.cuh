@@ -17,18 +17,24 @@ namespace mrt {
 
 #define MRT_STACK8 32          /* node groups; host checks the tree depth against it (api.cu) */
 
+// Visiting order of child slots per ray octant: lut[c][x] = x with bit i moved to bit i ^ c.  2 KB of shared memory,
+// filled once per block by the kernel (every thread of the block must call this) and handed to the traversal.
+#define MRT_ORDER_LUT_BYTES (8 * 256)
+__device__ __forceinline__ void bvh8_fill_order_lut(uint8_t* lut) {
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) lut[i] = (uint8_t)mrt_perm8(i & 0xffu, i >> 8);
+    __syncthreads();
+}
+
 template <class IO, bool COUNT = false>
 __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nodes8, const float4* __restrict__ tris,
                                                   uint32_t total, unsigned int* head, uint32_t refillBelow, uint32_t leafMin,
-                                                  uint32_t magic, IO& io, unsigned long long* visits = nullptr) {
+                                                  uint32_t magic, const uint8_t* orderLut, IO& io,
+                                                  unsigned long long* visits = nullptr) {
     // COUNT: diagnostic build that adds up node tests and triangle tests into visits[0], visits[1] (MRT_TRACE_COUNT=1)
     uint32_t nNodes = 0, nTris = 0;
     // magic = 0x47000000 arrives as a kernel PARAMETER: were it a literal, ptxas would make it PRMT's immediate and
     // spend an extra move per plane on the byte selector instead (bvh8.h: mrt_plane)
-    // visiting order of child slots per ray octant: lut[c][x] = x with bit i moved to bit i ^ c
-    __shared__ uint8_t orderLut[8 * 256];
-    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) orderLut[i] = (uint8_t)mrt_perm8(i & 0xffu, i >> 8);
-    __syncthreads();
+    // orderLut: the block's shared-memory table filled by bvh8_fill_order_lut
     const uint32_t lane = threadIdx.x & 31u;
     const float tiny = 1e-30f;
     // leafMin carries the vote tuning: bits 0-7 = lanes with triangles that force a triangle step, bits 8-15 = ratio r
@@ -150,15 +156,13 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
 template <class IO, bool COUNT = false>
 __device__ __forceinline__ void trace_persistent8d(const float4* __restrict__ nodes8, const float4* __restrict__ tris,
                                                   uint32_t total, unsigned int* head, uint32_t refillBelow, uint32_t leafMin,
-                                                  uint32_t magic, IO& io, unsigned long long* visits = nullptr) {
+                                                  uint32_t magic, const uint8_t* orderLut, IO& io,
+                                                  unsigned long long* visits = nullptr) {
     // COUNT: diagnostic build that adds up node tests and triangle tests into visits[0], visits[1] (MRT_TRACE_COUNT=1)
     uint32_t nNodes = 0, nTris = 0;
     // magic = 0x47000000 arrives as a kernel PARAMETER: were it a literal, ptxas would make it PRMT's immediate and
     // spend an extra move per plane on the byte selector instead (bvh8.h: mrt_plane)
-    // visiting order of child slots per ray octant: lut[c][x] = x with bit i moved to bit i ^ c
-    __shared__ uint8_t orderLut[8 * 256];
-    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) orderLut[i] = (uint8_t)mrt_perm8(i & 0xffu, i >> 8);
-    __syncthreads();
+    // orderLut: the block's shared-memory table filled by bvh8_fill_order_lut
     const uint32_t lane = threadIdx.x & 31u;
     const float tiny = 1e-30f;
     // leafMin carries the vote tuning: bits 0-7 = lanes with triangles that force a triangle step, bits 8-15 = ratio r

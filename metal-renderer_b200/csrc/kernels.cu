@@ -8,7 +8,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false (see device_math.cuh for why).
 #include <cstdlib>
 #include "kernels.h"
-#include "device_trace.cuh"
+#include "device_trace8.cuh"
 
 namespace mrt {
 
@@ -176,8 +176,24 @@ __global__ void __launch_bounds__(256) k_display(const float4* __restrict__ imag
 // sequence of float operations per pixel is exactly the stage sequence of Renderer.mm:504-584.
 enum { PH_GEN = 0, PH_PRIMARY = 1, PH_SHADOW = 2 };
 
-template <bool COUNT, int MINB>
-__global__ void __launch_bounds__(256, MINB) k_render_fused(RenderParams P) {
+// WIDE: the traversal site is the wavefront pipeline's own core (device_trace8.cuh: 8-wide quantised tree, vote
+// scheduling) run over the warp's 32 rays without refill, so that megakernel and wavefront differ in the SCHEDULE only.
+// The 32 "work items" of a call are the warp's lanes; a warp-private counter in shared memory stands in for the queue head.
+struct FusedIO {
+    f3 o, d; bool want; HitRec out;
+    __device__ __forceinline__ bool load(uint32_t, TraceJob& job) {
+        if (!want) return false;
+        job.o = o; job.d = d; job.tmin = 0.0f; job.tmax = INFINITY; job.target = MRT_NO_HIT; job.tag = 0;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t, uint32_t, const HitRec& h) { out = h; }
+};
+
+template <bool COUNT, int MINB, bool WIDE>
+__global__ void __launch_bounds__(256, MINB) k_render_fused(RenderParams P, uint32_t leafMin, uint32_t magic) {
+    __shared__ uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 1];
+    __shared__ unsigned int warpHead[8];
+    if (WIDE) bvh8_fill_order_lut(orderLut);
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t tilesX = (P.g.W + 7u) >> 3;
@@ -215,10 +231,21 @@ __global__ void __launch_bounds__(256, MINB) k_render_fused(RenderParams P) {
             }
         }
         if (__all_sync(0xffffffffu, done)) break;
-        if (done) continue;
-
         const f3 dir = phase == PH_PRIMARY ? st.direction : sh.direction;
-        HitRec hit = trace_nearest<false>(P.S.nodes, P.S.tris, st.origin, dir, 0.0f, INFINITY, &dummyA, &dummyB);
+        HitRec hit;
+        if (WIDE) {                                       // warp-collective: finished lanes come along without a ray
+            FusedIO io; io.o = st.origin; io.d = dir; io.want = !done;
+            io.out.t = -1.0f; io.out.tri = MRT_NO_HIT; io.out.u = io.out.v = 0.0f;
+            if (lane == 0) warpHead[threadIdx.x >> 5] = 0u;
+            __syncwarp();
+            trace_persistent8(P.S.nodes8, P.S.tris8, 32u, &warpHead[threadIdx.x >> 5], 32u, leafMin, magic, orderLut, io);
+            __syncwarp();
+            hit = io.out;
+            if (done) continue;
+        } else {
+            if (done) continue;
+            hit = trace_nearest<false>(P.S.nodes, P.S.tris, st.origin, dir, 0.0f, INFINITY, &dummyA, &dummyB);
+        }
 
         bool finished = false;
         if (phase == PH_PRIMARY) {
@@ -292,22 +319,41 @@ void launch_display(cudaStream_t s, const float4* image, const float4* ref, floa
                     uint32_t RH, uint32_t toneMapping, uint32_t manualSRGB, uint32_t mode, float scale) {
     k_display<<<blocks_for(W * H), 256, 0, s>>>(image, ref, out, W, H, RW, RH, toneMapping, manualSRGB, mode, scale);
 }
+static int fused_bvh_width() {          // MRT_FUSED_BVH=2 keeps the megakernel on the binary tree (A/B runs); default 8
+    static const int w = [] { const char* e = getenv("MRT_FUSED_BVH"); return (e && atoi(e) == 2) ? 2 : 8; }();
+    return w;
+}
 void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays) {
     uint32_t tilesX = (p.g.W + 7u) >> 3, tilesY = (p.ownedRows + 3u) >> 2;
     uint32_t warps = tilesX * tilesY;
     if (warps == 0 || p.nFrames == 0) return;
     uint32_t blocks = (warps + 7u) / 8u;
-    static const int minb = [] { const char* e = getenv("MRT_FUSED_MINBLOCKS"); int v = e ? atoi(e) : 2; return v; }();
-    if (minb >= 4)      { if (countRays) k_render_fused<true, 4><<<blocks, 256, 0, s>>>(p); else k_render_fused<false, 4><<<blocks, 256, 0, s>>>(p); }
-    else if (minb == 3) { if (countRays) k_render_fused<true, 3><<<blocks, 256, 0, s>>>(p); else k_render_fused<false, 3><<<blocks, 256, 0, s>>>(p); }
-    else                { if (countRays) k_render_fused<true, 2><<<blocks, 256, 0, s>>>(p); else k_render_fused<false, 2><<<blocks, 256, 0, s>>>(p); }
+    // blocks per SM: 3 on the wide core (80 registers with some spill beat 127 registers at 2 blocks, pass AB: +17 % / +11 %)
+    static const int minb = [] { const char* e = getenv("MRT_FUSED_MINBLOCKS"); int v = e ? atoi(e) : (fused_bvh_width() == 8 ? 3 : 2); return v; }();
+    // vote tuning of the wide traversal core, packed as in launch_wf_trace (wavefront.cu): 8 lanes / ratio 6
+    static const uint32_t leafMin = [] {
+        const char* a = getenv("MRT_TRACE_LEAFMIN"); const char* b = getenv("MRT_TRACE_TRIRATIO");
+        int l = a ? atoi(a) : 8, r = b ? atoi(b) : 6;
+        return (uint32_t)(l < 1 ? 1 : (l > 32 ? 32 : l)) | ((uint32_t)(r < 0 ? 0 : (r > 255 ? 255 : r)) << 8);
+    }();
+    const uint32_t magic = 0x47000000u;
+#define MRT_LAUNCH_FUSED(MB, WD) do { if (countRays) k_render_fused<true, MB, WD><<<blocks, 256, 0, s>>>(p, leafMin, magic); \
+                                      else k_render_fused<false, MB, WD><<<blocks, 256, 0, s>>>(p, leafMin, magic); } while (0)
+    if (fused_bvh_width() == 8) {
+        if (minb >= 4) MRT_LAUNCH_FUSED(4, true); else if (minb == 3) MRT_LAUNCH_FUSED(3, true); else MRT_LAUNCH_FUSED(2, true);
+    } else {
+        if (minb >= 4) MRT_LAUNCH_FUSED(4, false); else if (minb == 3) MRT_LAUNCH_FUSED(3, false); else MRT_LAUNCH_FUSED(2, false);
+    }
+#undef MRT_LAUNCH_FUSED
 }
 int fused_kernel_info(int* regs, int* maxBlocksPerSM) {
     cudaFuncAttributes a;
-    cudaError_t e = cudaFuncGetAttributes(&a, k_render_fused<true, 2>);
+    const bool wide = fused_bvh_width() == 8;
+    cudaError_t e = wide ? cudaFuncGetAttributes(&a, k_render_fused<true, 2, true>) : cudaFuncGetAttributes(&a, k_render_fused<true, 2, false>);
     if (e != cudaSuccess) return (int)e;
     *regs = a.numRegs;
-    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true, 2>, 256, 0);
+    return wide ? (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true, 2, true>, 256, 0)
+                : (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true, 2, false>, 256, 0);
 }
 
 }  // namespace mrt

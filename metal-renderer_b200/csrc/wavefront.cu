@@ -55,7 +55,9 @@ __global__ void __launch_bounds__(128, MINB) k_intersect_persistent(DeviceScene 
                                                                     bool useGrid, bool vec, unsigned long long* liveCounter,
                                                                     unsigned int* head, uint32_t refillBelow, uint32_t leafMin, uint32_t magic) {
     StridedIO io; io.rays = rays; io.stride = stride; io.out = out; io.g = g; io.useGrid = useGrid; io.vec = vec; io.live = 0;
-    if (WIDE) trace_persistent8(S.nodes8, S.tris8, count, head, refillBelow, leafMin, magic, io);
+    __shared__ uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 1];
+    if (WIDE) bvh8_fill_order_lut(orderLut);
+    if (WIDE) trace_persistent8(S.nodes8, S.tris8, count, head, refillBelow, leafMin, magic, orderLut, io);
     else trace_persistent(S.nodes, S.tris, count, head, refillBelow, leafMin, io);
     if (liveCounter) {
         uint32_t n = __reduce_add_sync(0xffffffffu, io.live);
@@ -101,10 +103,12 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     }
     WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
-    if (WIDE == 2) trace_persistent8d<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic, io,
-                                                   counters ? counters + 2 : nullptr);
-    else if (WIDE) trace_persistent8<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic, io,
-                                             counters ? counters + 2 : nullptr);
+    __shared__ uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 1];
+    if (WIDE) bvh8_fill_order_lut(orderLut);
+    if (WIDE == 2) trace_persistent8d<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic,
+                                                   orderLut, io, counters ? counters + 2 : nullptr);
+    else if (WIDE) trace_persistent8<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic,
+                                                  orderLut, io, counters ? counters + 2 : nullptr);
     else trace_persistent(S.nodes, S.tris, nExt + nShadow, b.heads + parity, refillBelow, leafMin, io);
 }
 
