@@ -78,7 +78,7 @@ struct mrt_ctx {
 
 static void free_scene(mrt_ctx* c) {
     cudaFree(c->dNodes); cudaFree(c->dTris); cudaFree(c->dShade); cudaFree(c->dMats); cudaFree(c->dLights); cudaFree(c->dCdf);
-    cudaFree(c->dTriSlot); cudaFree(c->dNodes8); cudaFree(c->dTris8);
+    cudaFree(c->dTriSlot); cudaFree(c->dNodes8);          // dTris8 lives in the same allocation
     c->dNodes8 = c->dTris8 = nullptr;
     c->dNodes = c->dTris = c->dShade = c->dMats = c->dLights = c->dCdf = c->dTriSlot = nullptr;
     c->wf.triSlot = nullptr; c->wf.triRecords = nullptr;
@@ -185,6 +185,36 @@ int mrt_destroy(mrt_ctx* c) {
     return MRT_OK;
 }
 
+// MRT_L2_PERSIST=1: keep the wide tree (and as much of its triangle records as fits) in the persisting part of L2, so
+// that the shade kernel's streaming between two trace launches does not evict it.  Window = [base, base + bytes)
+// clipped to the device's maximum; hit ratio = set-aside / window when the window is larger than the set-aside.
+static cudaError_t set_l2_window(mrt_ctx* c, void* base, size_t bytes) {
+    static const int on = [] { const char* e = getenv("MRT_L2_PERSIST"); return e ? atoi(e) : 0; }();
+    if (!on || bytes == 0) return cudaSuccess;
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, c->cfg.device);
+    if (e != cudaSuccess) return e;
+    if (prop.persistingL2CacheMaxSize <= 0 || prop.accessPolicyMaxWindowSize <= 0) return cudaSuccess;
+    size_t setAside = std::min<size_t>((size_t)prop.persistingL2CacheMaxSize, bytes);
+    if (on > 1) setAside = std::min<size_t>(setAside, (size_t)on << 20);          // MRT_L2_PERSIST=<MiB> caps the set-aside
+    e = cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, setAside);
+    if (e != cudaSuccess) return e;
+    cudaStreamAttrValue v;
+    std::memset(&v, 0, sizeof v);
+    v.accessPolicyWindow.base_ptr = base;
+    v.accessPolicyWindow.num_bytes = std::min<size_t>(bytes, (size_t)prop.accessPolicyMaxWindowSize);
+    v.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)setAside / (double)v.accessPolicyWindow.num_bytes);
+    v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    e = cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &v);
+    for (int g = 0; g < 4 && e == cudaSuccess; ++g) e = cudaStreamSetAttribute(c->groupStream[g], cudaStreamAttributeAccessPolicyWindow, &v);
+    if (getenv("MRT_L2_VERBOSE"))
+        fprintf(stderr, "mrt: L2 window %zu B, set-aside %zu B (device max %d B, max window %d B), hit ratio %.3f\n",
+                (size_t)v.accessPolicyWindow.num_bytes, setAside, prop.persistingL2CacheMaxSize, prop.accessPolicyMaxWindowSize,
+                v.accessPolicyWindow.hitRatio);
+    return e;
+}
+
 int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count, const uint32_t* indices, uint32_t triangle_count,
                   const mrt_triangle_reference* references, const mrt_material* materials, uint32_t material_count,
                   const mrt_light_triangle* lights, uint32_t light_count) {
@@ -258,8 +288,16 @@ int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count,
     Bvh8Result bvh8;
     build_bvh8(vertices, indices, triangle_count, c->cfg.bvh_threads, bvh8);
     NEED(bvh8.depth + 2 < 32, MRT_E_INVALID, "wide BVH depth %u exceeds traversal stack", bvh8.depth);
-    CK(upload(&c->dNodes8, bvh8.nodes.data(), bvh8.nodes.size() * sizeof(Bvh8Node)));
-    CK(upload(&c->dTris8, bvh8.tris.data(), bvh8.tris.size() * sizeof(BvhTri)));
+    {   // wide nodes and their triangle records share ONE allocation (nodes first), so that a single L2 access-policy
+        // window can cover what the trace kernel gathers from
+        const size_t nodeBytes = (bvh8.nodes.size() * sizeof(Bvh8Node) + 255) & ~size_t(255);
+        const size_t triBytes = bvh8.tris.size() * sizeof(BvhTri);
+        CK(cudaMalloc(&c->dNodes8, std::max<size_t>(nodeBytes + triBytes, 16)));
+        c->dTris8 = static_cast<char*>(c->dNodes8) + nodeBytes;
+        if (!bvh8.nodes.empty()) CK(cudaMemcpy(c->dNodes8, bvh8.nodes.data(), bvh8.nodes.size() * sizeof(Bvh8Node), cudaMemcpyHostToDevice));
+        if (triBytes) CK(cudaMemcpy(c->dTris8, bvh8.tris.data(), triBytes, cudaMemcpyHostToDevice));
+        CK(set_l2_window(c, c->dNodes8, nodeBytes + triBytes));
+    }
     c->S.nodes8 = (const float4*)c->dNodes8; c->S.tris8 = (const float4*)c->dTris8;
     const bool wide = trace_uses_wide_bvh();
     const std::vector<BvhTri>& order = wide ? bvh8.tris : bvh.tris;

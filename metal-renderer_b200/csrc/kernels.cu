@@ -319,8 +319,11 @@ void launch_display(cudaStream_t s, const float4* image, const float4* ref, floa
                     uint32_t RH, uint32_t toneMapping, uint32_t manualSRGB, uint32_t mode, float scale) {
     k_display<<<blocks_for(W * H), 256, 0, s>>>(image, ref, out, W, H, RW, RH, toneMapping, manualSRGB, mode, scale);
 }
-static int fused_bvh_width() {          // MRT_FUSED_BVH=2 keeps the megakernel on the binary tree (A/B runs); default 8
-    static const int w = [] { const char* e = getenv("MRT_FUSED_BVH"); return (e && atoi(e) == 2) ? 2 : 8; }();
+// MRT_FUSED_BVH=8 puts the megakernel on the wide traversal core (the like-for-like comparison with the wavefront
+// pipeline).  Default 2: the per-lane binary-tree loop, which shares neither tree nor traversal code with the
+// production path — that independence is what the "schedules agree" tests lean on.
+static int fused_bvh_width() {
+    static const int w = [] { const char* e = getenv("MRT_FUSED_BVH"); return (e && atoi(e) == 8) ? 8 : 2; }();
     return w;
 }
 void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays) {
