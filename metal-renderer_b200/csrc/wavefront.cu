@@ -105,7 +105,10 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
     __shared__ uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 1];
     if (WIDE) bvh8_fill_order_lut(orderLut);
-    if (WIDE == 2) trace_persistent8d<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic,
+    __shared__ TqWarp tq[WIDE == 3 ? 4 : 1];
+    if (WIDE == 3) trace_persistent8q<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic,
+                                                   orderLut, &tq[threadIdx.x >> 5], io, counters ? counters + 2 : nullptr);
+    else if (WIDE == 2) trace_persistent8d<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic,
                                                    orderLut, io, counters ? counters + 2 : nullptr);
     else if (WIDE) trace_persistent8<WfIO, COUNT>(S.nodes8, S.tris8, nExt + nShadow, b.heads + parity, refillBelow, leafMin, magic,
                                                   orderLut, io, counters ? counters + 2 : nullptr);
@@ -332,12 +335,12 @@ static int device_sms() {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     return n > 0 ? n : 148;
 }
-struct TraceTuning { int minb, refill, leafMin, wide, triRatio, defer, triThresh; };
+struct TraceTuning { int minb, refill, leafMin, wide, triRatio, defer, triThresh, tq; };
 static TraceTuning trace_tuning() {
     static const int wide = env_int("MRT_BVH_WIDTH", 8) == 8 ? 1 : 0;
     static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", wide ? 8 : 10), env_int("MRT_TRACE_REFILL", 24),
                                    env_int("MRT_TRACE_LEAFMIN", 8), wide, env_int("MRT_TRACE_TRIRATIO", 6),
-                                   env_int("MRT_TRACE_DEFER", 0), env_int("MRT_TRACE_TRITHRESH", 16) };
+                                   env_int("MRT_TRACE_DEFER", 0), env_int("MRT_TRACE_TRITHRESH", 16), env_int("MRT_TRACE_TQ", 0) };
     return t;
 }
 
@@ -376,7 +379,12 @@ void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     auto blocks = [&](int perSM) { uint32_t cap = (uint32_t)(device_sms() * perSM); return maxUseful < cap ? (maxUseful ? maxUseful : 1u) : cap; };
 #define MRT_LAUNCH_TRACE(MB, WD) k_wf_trace<MB, WD><<<blocks(MB), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters)
     // countVisits (mrt_set_profile bit 1 / MRT_TRACE_COUNT=1): diagnostic variant adding node / triangle tests into stats
-    if (t.wide && t.defer) {                                           // postponed triangles (device_trace8.cuh)
+    if (t.wide && t.tq && p.S.triangleCount < (1u << 27)) {            // warp-wide triangle queue (device_trace8.cuh); MRT_TRACE_TQ = pairs that trigger a triangle step
+        static const int tqWait = env_int("MRT_TRACE_TQWAIT", 8);      // waiting lanes that force a triangle step
+        const uint32_t th = (uint32_t)(t.tq < 1 ? 1 : (t.tq > 96 ? 96 : t.tq)) | ((uint32_t)(tqWait < 1 ? 1 : (tqWait > 33 ? 33 : tqWait)) << 8);
+        if (countVisits && p.counters) k_wf_trace<8, 3, true><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, th, 0x47000000u, p.counters);
+        else k_wf_trace<8, 3><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, th, 0x47000000u, p.counters);
+    } else if (t.wide && t.defer) {                                    // postponed triangles (device_trace8.cuh)
         if (countVisits && p.counters) k_wf_trace<8, 2, true><<<blocks(8), 128, 0, s>>>(p.S, b, parity, refill, leafMin, 0x47000000u, p.counters);
         else MRT_LAUNCH_TRACE(8, 2);
     } else if (t.wide && countVisits && p.counters) {

@@ -1,0 +1,10 @@
+#!/bin/bash
+# round-1 GPU pass AH: ncu of one steady-state trace launch, production kernel vs triangle-queue variant
+mkdir -p gpurun_out
+R=./metal-renderer_b200/bin/mrt_render
+S="--scene spheres-1m --size 1920x1080 --seed 3 --frames 8 --pipeline wavefront"
+for v in 0 24; do
+MRT_TRACE_TQ=$v timeout 300 $R $S > /dev/null 2>&1 && \
+MRT_TRACE_TQ=$v timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_wf_trace -s 30 -c 1 -f -o gpurun_out/prof_ah_tq$v $R $S > gpurun_out/ncu_ah_tq$v.log 2>&1
+done
+ls -la gpurun_out/*.ncu-rep
