@@ -42,6 +42,8 @@ struct Bvh8Result {
     uint32_t depth = 0;             // levels of wide nodes
     float sah_cost = 0.0f;
     double build_ms = 0.0;
+    int bins = 16;                  // SAH bins per axis the binary builder used (build_bvh8 picks among candidates)
+    float sample_cost = 0.0f;       // node tests + 1.2 x triangle tests per ray of the selection sample (0 = no selection)
 };
 
 // Collapse + quantise.  Same inputs as build_bvh; deterministic for any thread count.

@@ -95,6 +95,7 @@ print("variant ok", sa["kernel_launches"])
     {"MRT_WF_SLOTS": "2"}, {"MRT_WF_SLOTS": "3", "MRT_WF_SPLIT": "2"},  # more path slots than pixels (fewer, larger waves)
     {"MRT_BVH8_MAXLEAF": "1"}, {"MRT_BVH8_CPRIM": "0.3", "MRT_BVH8_FRONTLEAF": "3"},     # other shapes of the wide tree
     {"MRT_TRACE_TQ": "32"}, {"MRT_TRACE_TQ": "1"}, {"MRT_TRACE_TQ": "96", "MRT_TRACE_COUNT": "1"},   # warp-wide triangle queue
+    {"MRT_BVH_BINS": "64"}, {"MRT_BVH_BINS": "8,32"},                   # SAH bins of the binary builder: fixed / other candidates for the sampled selection
     {"MRT_FUSED_BVH": "8"}, {"MRT_FUSED_BVH": "8", "MRT_FUSED_MINBLOCKS": "2"},   # megakernel on the wide traversal core (default: binary tree)
 ], ids=lambda e: ",".join(f"{k[4:].lower()}={v}" for k, v in e.items()))
 def test_tuning_switches_do_not_change_the_bits(env):
