@@ -394,4 +394,16 @@ def main():
 
 
 if __name__ == "__main__":
+    # The contract is ONE line on stdout.  Libraries write there too (NCCL prints its version banner on rank 0 when the
+    # box sets NCCL_DEBUG), so everything but the result line goes to stderr: fd 1 is pointed at fd 2 for the run and the
+    # JSON line is written to the saved descriptor.
+    sys.stdout.flush()
+    _real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    _print = print
+
+    def print(*a, **k):       # noqa: A001 — the result lines of run_ours / run_reference
+        k.pop("flush", None)
+        _print(*a, file=_real_stdout, **k)
+        _real_stdout.flush()
     main()
