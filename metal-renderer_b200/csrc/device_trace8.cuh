@@ -39,7 +39,7 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
     const float tiny = 1e-30f;
     // leafMin carries the vote tuning: bits 0-7 = lanes with triangles that force a triangle step, bits 8-15 = ratio r
     // (triangle step as soon as 16 * lanes-with-triangles >= r * lanes-with-node-work; 0 = off).  A triangle step
-    // costs ~0.4 node steps, so r = 6 picks whichever step advances more lanes per instruction (pass M: +2 %; an L1
+    // costs ~0.4 node steps, so r = 6..7 picks whichever step advances more lanes per instruction (pass M: +2 %; an L1
     // prefetch of the leaf's first triangle at the end of the node step was tried there too and lost 1-20 %).
     const int triRatio = int((leafMin >> 8) & 0xffu);
     leafMin &= 0xffu;
@@ -397,7 +397,7 @@ __device__ __forceinline__ void trace_persistent8d(const float4* __restrict__ no
     const float tiny = 1e-30f;
     // leafMin carries the vote tuning: bits 0-7 = lanes with triangles that force a triangle step, bits 8-15 = ratio r
     // (triangle step as soon as 16 * lanes-with-triangles >= r * lanes-with-node-work; 0 = off).  A triangle step
-    // costs ~0.4 node steps, so r = 6 picks whichever step advances more lanes per instruction (pass M: +2 %; an L1
+    // costs ~0.4 node steps, so r = 6..7 picks whichever step advances more lanes per instruction (pass M: +2 %; an L1
     // prefetch of the leaf's first triangle at the end of the node step was tried there too and lost 1-20 %).
     const int triRatio = int((leafMin >> 8) & 0xffu);
     const int triThresh = int((leafMin >> 18) & 0x3fu) ? int((leafMin >> 18) & 0x3fu) : 16;    // bits 18-23: see below

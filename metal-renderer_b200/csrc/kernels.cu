@@ -333,10 +333,10 @@ void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays) 
     uint32_t blocks = (warps + 7u) / 8u;
     // blocks per SM: 3 on the wide core (80 registers with some spill beat 127 registers at 2 blocks, pass AB: +17 % / +11 %)
     static const int minb = [] { const char* e = getenv("MRT_FUSED_MINBLOCKS"); int v = e ? atoi(e) : (fused_bvh_width() == 8 ? 3 : 2); return v; }();
-    // vote tuning of the wide traversal core, packed as in launch_wf_trace (wavefront.cu): 8 lanes / ratio 6
+    // vote tuning of the wide traversal core, packed as in launch_wf_trace (wavefront.cu): 10 lanes / ratio 7
     static const uint32_t leafMin = [] {
         const char* a = getenv("MRT_TRACE_LEAFMIN"); const char* b = getenv("MRT_TRACE_TRIRATIO");
-        int l = a ? atoi(a) : 8, r = b ? atoi(b) : 6;
+        int l = a ? atoi(a) : 10, r = b ? atoi(b) : 7;
         return (uint32_t)(l < 1 ? 1 : (l > 32 ? 32 : l)) | ((uint32_t)(r < 0 ? 0 : (r > 255 ? 255 : r)) << 8);
     }();
     const uint32_t magic = 0x47000000u;

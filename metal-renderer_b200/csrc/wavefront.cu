@@ -339,7 +339,7 @@ struct TraceTuning { int minb, refill, leafMin, wide, triRatio, defer, triThresh
 static TraceTuning trace_tuning() {
     static const int wide = env_int("MRT_BVH_WIDTH", 8) == 8 ? 1 : 0;
     static const TraceTuning t = { env_int("MRT_TRACE_MINBLOCKS", wide ? 8 : 10), env_int("MRT_TRACE_REFILL", 24),
-                                   env_int("MRT_TRACE_LEAFMIN", 8), wide, env_int("MRT_TRACE_TRIRATIO", 6),
+                                   env_int("MRT_TRACE_LEAFMIN", 10), wide, env_int("MRT_TRACE_TRIRATIO", 7),
                                    env_int("MRT_TRACE_DEFER", 0), env_int("MRT_TRACE_TRITHRESH", 16), env_int("MRT_TRACE_TQ", 0) };
     return t;
 }
