@@ -44,10 +44,31 @@ BYTES_PER_SAMPLE = 140       # raygen 16+80, accumulate 12+16+16
 BYTES_PER_RAY_TRACE = 48     # one intersect: 32 B of ray read + 16 B Intersection written
 NODE_BYTES = 80              # 8-wide quantised node (csrc/bvh8.h)
 TRIANGLE_RECORD_BYTES = 48   # leaf-ordered triangle record (csrc/bvh.h)
-# from profiles/r1_x_wf_trace_steady_ncu_summary.txt (ncu --set full of one steady-state k_wf_trace launch — every slot
-# busy, mixed bounce depths — 1M triangles, 1080p)
-NCU_TRACE_DRAM_BYTES_PER_LAUNCH = 465_602_816       # 416.85 MB read + 48.75 MB written
-NCU_TRACE_ISSUE_ACTIVE = 0.695
+PARITY_FRAMES = {"spheres-10m-4k": 1}     # frames of the untimed parity step (default 2); the oracle renders them on the host cores
+
+
+def ncu_summary(kernel, workload):
+    """Counters of one steady-state launch of `kernel` ("trace" / "shade") on `workload`, parsed from the committed
+    summary profiles/ncu_<kernel>_<workload>.txt (written by scripts/ncu_collect.py from an `ncu --set full` report of
+    HEAD's kernels).  None when there is no capture of this workload — never a number from another scene."""
+    path = ROOT / "profiles" / f"ncu_{kernel}_{workload}.txt"
+    if not path.exists():
+        return None
+    out = {"source": str(path.relative_to(ROOT))}
+    for line in path.read_text().splitlines():
+        parts = line.split()
+        if line.startswith("#"):
+            if "commit" in parts:
+                out["commit"] = parts[parts.index("commit") + 1]
+            if "rays_in_launch" in parts:
+                out["rays_in_launch"] = float(parts[parts.index("rays_in_launch") + 1])
+            continue
+        if len(parts) >= 2:
+            try:
+                out[parts[0]] = float(parts[1].replace(",", ""))
+            except ValueError:
+                pass
+    return out
 
 
 def measured_peaks():
@@ -184,9 +205,76 @@ def cpu_baseline(wl, m, scene, budget_s=15.0):
 
 
 # ------------------------------------------------------------------------------------------------------------------
+def rel_rmse(got, want):
+    ok = np.isfinite(got).all(axis=-1) & np.isfinite(want).all(axis=-1)
+    a, b = got[ok].astype(np.float64), want[ok].astype(np.float64)
+    return float(np.sqrt(np.mean((a - b) ** 2)) / max(np.sqrt(np.mean(b ** 2)), 1e-30)), float(ok.mean())
+
+
+def parity_step(args, wl, m, D, scene, r, ep, coll, rank, world):
+    """Untimed: the gates of BASELINE.md 3 on the benchmarked workload, against the oracle on the host cores (rank 0).
+    N = 1: `k` frames at full size — primary-hit triangle ids of every pixel and the accumulated image.
+    N > 1: one ShardedRenderer step of k frames per rank; the all-reduced image is held against the oracle's SEQUENTIAL
+    render of the same k*N frames on the rows y % stride == 0 (stride bounds the oracle's work), and the primary hits
+    of frame 0 on every pixel."""
+    import torch
+    sys.path.insert(0, str(ROOT / "oracle"))
+    W, H, D_, seed = wl["width"], wl["height"], wl["depth"], wl["seed"]
+    k = PARITY_FRAMES.get(args.workload, 2)
+    init = m.noise_tile(seed, 0xFFFFFFFF)
+    r.sync()
+    r.clear_image()
+    for s in range(3):
+        r.update_noise(s, init)
+    # primary hits through the staged entry points (raygen + intersect of frame 0)
+    r.raygen(0); r.intersect(m.BUF_RAYS)
+    hits = r.read_buffer(m.BUF_INTERSECTIONS)["triangleIndex"].copy() if rank == 0 else None
+    frames = k * world
+    sr = D.ShardedRenderer(ep, rank, world, coll, mode="samples")        # fresh accumulation state (world 1: running mean)
+    plan = D.plan_sample_shard(0, k, rank, world)
+    tiles = m.noise_tiles(seed, plan.first_frame, plan.span)
+    lead = {f: m.noise_tile(seed, f) for f in D.lead_in_frames(plan.first_frame)}
+    if world > 1:
+        r.clear_image()
+    sr.step(k, tiles, lead_in=lead, sync=True)
+    got = ep.read(sr.output()).copy()
+    out = None
+    if rank == 0:
+        import oracle as orc
+        t0 = time.perf_counter()
+        stride = 1 if world == 1 else max(1, min(16, world))
+        o = orc.Oracle(max_path_length=D_, threads=0)
+        o.init_raytracing(scene)
+        o.drawable_size_will_change(W, H)
+        for s in range(3):
+            o.update_noise(s, init)
+        o.raygen(0); o.intersect(0)
+        want_hits = o.read_buffer(2)["triangleIndex"]
+        agree = float(np.mean(hits == want_hits))
+        if stride > 1:
+            o.set_row_shard(0, stride)
+        o.draw(frames, m.noise_tiles(seed, 0, frames))
+        want = o.save_current_image()
+        rr, finite = rel_rmse(got[::stride, :, :3], want[::stride, :, :3])
+        same_bits = float(np.mean(got[::stride].view(np.uint32) == want[::stride].view(np.uint32)))
+        out = {"hit_id_agree": agree, "rrmse": rr, "frames": frames, "pixels": int(W * H), "rows_compared": int(len(range(0, H, stride))),
+               "image_words_bit_equal": same_bits, "finite_pixels": finite, "oracle_threads": o.threads,
+               "oracle_s": time.perf_counter() - t0,
+               "gates": {"hit_id_agree_min": 0.9999, "rrmse_max": 1e-3},
+               "pass": bool(agree >= 0.9999 and rr <= 1e-3),
+               "what": ("wavefront pipeline vs oracle, same frames, full image" if world == 1 else
+                        f"all-reduced image of one {world}-rank step vs the oracle's sequential render of the same {frames} frames on rows y % {stride} == 0")}
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    del torch
+    return out
+
+
 def run_ours(args, wl):
     import torch
     import mrt_b200 as m
+    from mrt_b200 import distributed as D
     rank, local_rank, world = dist_env()
     if world > 1:
         import torch.distributed as dist
@@ -194,49 +282,45 @@ def run_ours(args, wl):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = local_rank
     torch.cuda.set_device(dev)
-    W, H, F, D = wl["width"], wl["height"], wl["frames"], wl["depth"]
+    W, H, F, Dp = wl["width"], wl["height"], wl["frames"], wl["depth"]
+    t_setup = time.perf_counter()
     scene = m.Scene.procedural(wl["scene"], wl["seed"])
-    r = m.Renderer(device=dev, max_path_length=D, accumulate_mode=m.ACCUM_SUM if world > 1 else m.ACCUM_MEAN)
+    t_scene = time.perf_counter()
+    r = m.Renderer(device=dev, max_path_length=Dp)
     r.init_raytracing(scene)
     r.drawable_size_will_change(W, H)
+    r.sync()
+    setup_ms = {"scene_generation": (t_scene - t_setup) * 1e3, "bvh_build_upload_resize": (time.perf_counter() - t_scene) * 1e3}
     init = m.noise_tile(wl["seed"], 0xFFFFFFFF)
     for s in range(3):
         r.update_noise(s, init)
+    ep = D.CudaEndpoint(r, dev)
+    coll = D.TorchCollective()
 
-    from mrt_b200.distributed import lead_in_frames, plan_sample_shard
     n_tiles = F * world                               # tile j belongs to frame (step start + j); reused every step
     span = (F - 1) * world + 1                        # tiles one rank consumes: frames first .. first+(F-1)*world
     host_tiles = torch.empty((n_tiles, m.NOISE_TILE_FLOATS), dtype=torch.float32, pin_memory=True)
     m.noise_tiles(wl["seed"], 0, n_tiles, out=host_tiles.numpy())
     dev_tiles = host_tiles.to(f"cuda:{dev}")
     host_image = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
-    img_ptr, img_bytes = r.image_device_ptr()
-
-    class _Img:
-        __cuda_array_interface__ = {"shape": (H, W, 4), "typestr": "<f4", "data": (img_ptr, False), "version": 2}
-    image_t = torch.as_tensor(_Img(), device=f"cuda:{dev}") if world > 1 else None
     torch.cuda.synchronize()
-
-    state = {"frame": 0}
-
     tile_bytes = m.NOISE_TILE_FLOATS * 4
 
-    def step(tiles_ptr, readback):
-        plan = plan_sample_shard(state["frame"], F, rank, world)
-        first = plan.first_frame
-        if world > 1:
-            for f in lead_in_frames(first):           # slots of the two frames before this rank's first one
-                r.update_noise_from(f % 3, tiles_ptr + ((f - state["frame"]) % n_tiles) * tile_bytes)
-            r.clear_image()
-        r.draw(F, tiles_ptr + rank * tile_bytes, first_frame=first, frame_stride=world, sync=False)
-        if world > 1:
-            r.sync()
-            dist.all_reduce(image_t)                  # one NCCL sum of the W*H*float4 image per step
-            torch.cuda.current_stream().synchronize()
-            r.scale_image(1.0 / (F * world))
-        if readback:
-            r.read_image_into(host_image.data_ptr())  # D2H + sync
-        state["frame"] += F * world
+    def make_stepper(frames_per_rank):
+        """One step = ShardedRenderer.step (mrt_b200/distributed.py — the code the sharding tests run): `frames_per_rank`
+        frames on every rank, one NCCL all-reduce of the sum image, normalisation.  Tiles are addressed inside the
+        resident (device) or pinned (host) tile array: tile j = frame (step start + j) modulo the array."""
+        sr = D.ShardedRenderer(ep, rank, world, coll, mode="samples")
+        n = frames_per_rank * world
+
+        def step(tiles_ptr, readback):
+            start = sr.next_frame
+            plan = D.plan_sample_shard(start, frames_per_rank, rank, world)
+            lead = {f: tiles_ptr + ((f - start) % n) * tile_bytes for f in D.lead_in_frames(plan.first_frame)} if world > 1 else None
+            sr.step(frames_per_rank, tiles_ptr + rank * tile_bytes, lead_in=lead)
+            if readback:
+                ep.read(sr.output(), host_image)      # D2H of the job's image + sync
+        return sr, step
 
     def barrier():
         r.sync()
@@ -244,20 +328,14 @@ def run_ours(args, wl):
         if world > 1:
             dist.barrier()
 
-    def max_over_ranks(x):
+    def reduce_ranks(x, op="max"):
         if world == 1:
             return x
         t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{dev}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
         return float(t.item())
 
-    def sum_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{dev}")
-        dist.all_reduce(t)
-        return float(t.item())
-
+    sr, step = make_stepper(F)
     for _ in range(max(args.warmup, 3)):
         step(dev_tiles.data_ptr(), False)
     barrier()
@@ -277,28 +355,28 @@ def run_ours(args, wl):
         wall_ms = (time.perf_counter() - t0) * 1e3
         dev_ms = r.event_elapsed_ms(0, 1)
     st = r.stats()
-    ms = max_over_ranks(dev_ms)
+    ms = reduce_ranks(dev_ms)
     rays_local = st["primary_rays"] + st["shadow_rays"]
-    rays = sum_over_ranks(rays_local)
-    segments = sum_over_ranks(st["primary_rays"])
+    rays = reduce_ranks(rays_local, "sum")
     samples = float(W) * H * F * world * args.steps
     value = rays / (ms * 1e-3) / 1e6
     launches = st["kernel_launches"]
-    kernel_ms = st["last_kernel_ms"]
     trace_ms, trace_launches = st["profile_trace_ms"], st["profile_trace_launches"]      # last step of the timed region
+    tail_waves = st["tail_waves"]
     r.set_profile(0)
 
-    # ---- e2e: host buffers, H2D of the noise tiles and D2H of the image inside every step ------------------------
-    step(host_tiles.data_ptr(), True)        # untimed: first use of the H2D / D2H path (the W warm-up steps above ran resident)
+    # ---- e2e: host buffers, H2D of the noise tiles and D2H of the image inside every step; default schedule (one CUDA
+    # graph per batch, no per-launch events) ------------------------------------------------------------------------
+    step(host_tiles.data_ptr(), True)        # untimed: first use of the H2D / D2H path and of the wave graph
     barrier()
     r.reset_stats()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step(host_tiles.data_ptr(), True)
     barrier()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_s = reduce_ranks(time.perf_counter() - t0)
     st2 = r.stats()
-    e2e_rays = sum_over_ranks(st2["primary_rays"] + st2["shadow_rays"])
+    e2e_rays = reduce_ranks(st2["primary_rays"] + st2["shadow_rays"], "sum")
     finite = bool(torch.isfinite(host_image[..., :3]).float().mean().item() > 0.999)
 
     # ---- untimed: one more step through the COUNTING variant of the trace kernel — node tests and triangle tests per ray
@@ -314,6 +392,40 @@ def run_ours(args, wl):
     node_tests_per_ray = st3["nodes_visited"] / counted_rays
     tri_tests_per_ray = st3["triangles_tested"] / counted_rays
 
+    # ---- strong scaling (N > 1): the SAME `frames` samples per pixel split over the ranks ---------------------------
+    strong = None
+    if world > 1 and not args.no_strong:
+        fs = max(1, F // world)
+        sr_s, step_s = make_stepper(fs)
+        sr_s.time_events = (2, 3)                      # CUDA events on the ctx stream around the collective
+        for _ in range(3):
+            step_s(dev_tiles.data_ptr(), False)
+        barrier()
+        r.reset_stats()
+        r.set_profile(m.PROFILE_TRACE_TIME)
+        ar_ms = []
+        r.event_record(4)
+        for _ in range(args.steps):
+            step_s(dev_tiles.data_ptr(), False)
+            r.sync()
+            ar_ms.append(r.event_elapsed_ms(2, 3))
+        r.event_record(5)
+        barrier()
+        s_ms = reduce_ranks(r.event_elapsed_ms(4, 5))
+        sts = r.stats()
+        r.set_profile(0)
+        s_rays = reduce_ranks(sts["primary_rays"] + sts["shadow_rays"], "sum")
+        strong = {"frames_total_per_step": fs * world, "frames_per_gpu": fs, "ms_total": s_ms / args.steps,
+                  "mrays_per_s": s_rays / (s_ms * 1e-3) / 1e6, "msamples_per_s": float(W) * H * fs * world * args.steps / (s_ms * 1e-3) / 1e6,
+                  "allreduce_ms": reduce_ranks(float(np.median(ar_ms))), "allreduce_bytes": int(W * H * 16),
+                  "waves": sts["waves_traced"], "tail_waves": sts["tail_waves"],
+                  "bvh_build_ms": reduce_ranks(st["bvh_build_ms"] + st["bvh8_build_ms"]),
+                  "note": "same samples per pixel as one GPU's step, split over the ranks (frames_per_gpu = frames / N); ms_total is "
+                          "the device time of a step incl. the all-reduce, max over ranks; allreduce_ms is the event-timed collective "
+                          "incl. the wait for the slowest rank; tail_waves = waves with fewer extension rays than half the path slots"}
+
+    parity = None if args.no_parity else parity_step(args, wl, m, D, scene, r, ep, coll, rank, world)
+
     if rank == 0:
         peak, peak_kind = measured_peaks()
         # dominant kernel = k_wf_trace.  SURVEY 8(d): per ray it reads 32 B of ray and writes a 16-B Intersection (48 B for
@@ -324,11 +436,29 @@ def run_ours(args, wl):
         alg_bytes_step = BYTES_PER_SAMPLE * W * H * F + BYTES_PER_SEGMENT * st["primary_rays"] / args.steps
         trace_launches = max(trace_launches, 1)
         bvh_bytes_per_ray = node_tests_per_ray * NODE_BYTES + tri_tests_per_ray * TRIANGLE_RECORD_BYTES
-        stream_bytes = BYTES_PER_RAY_TRACE * rays_per_step / trace_launches
-        alg_bytes = (BYTES_PER_RAY_TRACE + bvh_bytes_per_ray) * rays_per_step / trace_launches
+        rays_per_launch = rays_per_step / trace_launches
+        stream_bytes = BYTES_PER_RAY_TRACE * rays_per_launch
+        alg_bytes = (BYTES_PER_RAY_TRACE + bvh_bytes_per_ray) * rays_per_launch
         per_launch_ms = trace_ms / trace_launches
         achieved = alg_bytes / max(per_launch_ms * 1e-3, 1e-12) / 1e9
         achieved_stream = stream_bytes / max(per_launch_ms * 1e-3, 1e-12) / 1e9
+        # what ncu saw on HEAD's kernels for this workload (profiles/ncu_{trace,shade}_<workload>.txt), or null
+        nt, ns = ncu_summary("trace", args.workload), ncu_summary("shade", args.workload)
+        traffic = issue = None
+        if nt:
+            traffic = nt.get("dram__bytes_read.sum", 0.0) + nt.get("dram__bytes_write.sum", 0.0)
+            ia = nt.get("smsp__issue_active.avg.pct_of_peak_sustained_active")
+            lanes = nt.get("smsp__thread_inst_executed_per_inst_executed.ratio")
+            inst = nt.get("smsp__inst_executed.sum")
+            issue = {"warp_inst_per_launch": inst, "issue_active": ia / 100.0 if ia is not None else None, "lanes_per_inst": lanes,
+                     "thread_issue_frac": (ia / 100.0) * (lanes / 32.0) if ia is not None and lanes else None,
+                     "thread_inst_per_ray": inst * lanes / nt["rays_in_launch"] if inst and lanes and nt.get("rays_in_launch") else None,
+                     "warp_inst_per_ray": inst / nt["rays_in_launch"] if inst and nt.get("rays_in_launch") else None,
+                     "rays_in_profiled_launch": nt.get("rays_in_launch"),
+                     "profiled_launch_ms": nt.get("gpu__time_duration.sum", 0.0) / 1e6 if nt.get("gpu__time_duration.sum") else None,
+                     "peak_thread_inst_per_s": 148 * 4 * 32 * 1.965e9,
+                     "note": "SURVEY 8(d): issue = warp instructions / (cycles x 4 schedulers x 148 SMs) = issue_active; x lanes/32 "
+                             "= share of the THREAD-instruction issue peak.  This, not `frac`, is the bound that binds"}
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -338,31 +468,43 @@ def run_ours(args, wl):
             "wall_ms_per_step": wall_ms / args.steps,
             "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int((span + (2 if world > 1 else 0)) * tile_bytes),
                     "d2h_bytes_per_step": int(host_image.numel() * 4), "msamples_per_s": samples / e2e_s / 1e6,
-                    "image_finite": finite},
+                    "image_finite": finite, "gpu_launches_per_step": int(st2["kernel_launches"] / args.steps),
+                    "schedule": "one CUDA graph per batch (WHILE node ends the wave loop on the device)"},
             "gpu_launches": int(launches),
             "clocks": clocks.summary(),
+            "parity": parity,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRACE_DRAM_BYTES_PER_LAUNCH,
+                         "traffic": traffic,
+                         "source": {"trace": nt and {k: nt.get(k) for k in ("source", "commit")}, "shade": ns and {k: ns.get(k) for k in ("source", "commit")}},
                          "peak_kind": peak_kind, "kernel": "k_wf_trace", "algorithmic_bytes_per_launch": alg_bytes,
                          "algorithmic_bytes_per_ray": {"ray_and_intersection": BYTES_PER_RAY_TRACE, "bvh_term": bvh_bytes_per_ray,
                                                        "node_tests": node_tests_per_ray, "triangle_tests": tri_tests_per_ray,
                                                        "node_bytes": NODE_BYTES, "triangle_record_bytes": TRIANGLE_RECORD_BYTES},
                          "stream_only": {"achieved": achieved_stream, "frac": achieved_stream / peak,
                                          "algorithmic_bytes_per_launch": stream_bytes},
-                         "launch_ms": per_launch_ms, "launches_per_step": trace_launches,
+                         "launch_ms": per_launch_ms, "launches_per_step": trace_launches, "rays_per_launch": rays_per_launch,
                          "kernel_share_of_step": trace_ms / max(dev_ms / args.steps, 1e-9),
+                         "in_kernel_mrays_per_s": rays_per_launch / max(per_launch_ms * 1e-3, 1e-12) / 1e6,
                          "step_algorithmic_bytes": alg_bytes_step,
                          "step_achieved_gbs": alg_bytes_step / (dev_ms / args.steps * 1e-3) / 1e9,
-                         "issue_slot_utilisation_ncu": NCU_TRACE_ISSUE_ACTIVE,
+                         "issue": issue,
+                         "shade": ns and {"launch_ms": ns.get("gpu__time_duration.sum", 0.0) / 1e6,
+                                          "dram_bytes": ns.get("dram__bytes_read.sum", 0.0) + ns.get("dram__bytes_write.sum", 0.0),
+                                          "dram_pct_of_peak": ns.get("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+                                          "lanes_per_inst": ns.get("smsp__thread_inst_executed_per_inst_executed.ratio")},
+                         "tail_waves_per_step": tail_waves,
                          "note": "algorithmic bytes per ray = 48 B (32 B ray + 16 B Intersection) + node tests x 80 B + triangle tests "
                                  "x 48 B (SURVEY 8d incl. its BVH/scene term; visit counts of this workload from the device "
                                  "counters, untimed extra step).  The gathers of the BVH term are served mostly by L1/L2 — "
-                                 "traffic = DRAM bytes of one full-size launch (ncu --set full, profiles/) is a tenth of the "
-                                 "algorithmic bytes — so frac is the contract's algorithmic-bytes rate over the HBM peak, not "
-                                 "DRAM utilisation (ncu: 4.5 %); stream_only counts the 48 B alone.  ncu shows the kernel bound by "
-                                 "instruction issue on the ALU pipe (issue slots 69 % busy, ALU pipe 61 %, 19 of 32 lanes active)"},
-            "bvh": {"nodes": st["bvh_nodes"], "depth": st["bvh_depth"], "sah_cost": st["bvh_sah_cost"], "build_ms": st["bvh_build_ms"]},
+                                 "`traffic` = DRAM bytes of one steady-state launch (ncu --set full, the file named in `source`; null "
+                                 "if this workload has no capture) — so `frac` is the contract's algorithmic-bytes rate over the HBM "
+                                 "peak, not DRAM utilisation, and it rises when the tree gets worse; `issue` is the bound that binds"},
+            "bvh": {"nodes": st["bvh_nodes"], "depth": st["bvh_depth"], "sah_cost": st["bvh_sah_cost"], "build_ms": st["bvh_build_ms"],
+                    "wide_nodes": st["bvh8_nodes"], "wide_depth": st["bvh8_depth"], "wide_build_ms": st["bvh8_build_ms"]},
+            "setup_ms": setup_ms,
         }
+        if strong is not None:
+            line["strong"] = strong
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl, m, scene)
         print(json.dumps(line), flush=True)
@@ -381,6 +523,8 @@ def main():
     ap.add_argument("--frames", type=int, default=0, help="override frames per step per GPU")
     ap.add_argument("--ref-frames", type=int, default=1, help="frames per step of the CPU reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the untimed parity step against the oracle")
+    ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the fixed-work (strong scaling) measurement")
     ap.add_argument("--no-trace-events", action="store_true",
                     help="diagnostic: timed region without the per-launch event pairs (the roofline object is then meaningless)")
     args = ap.parse_args()

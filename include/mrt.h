@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define MRT_VERSION 100
+#define MRT_VERSION 101
 
 enum {
     MRT_OK = 0,
@@ -95,6 +95,10 @@ typedef struct mrt_stats {
     uint32_t bvh8_depth;
     float    profile_trace_ms;  /* mrt_set_profile(1): summed CUDA-event time of the k_wf_trace launches of the last mrt_render_frames */
     uint32_t profile_trace_launches;   /* ... and how many of them found work (queue not empty) */
+    float    bvh8_build_ms;     /* host wall time of the wide-tree build (all SAH-bin candidates + the sampled selection) */
+    uint32_t waves_traced;      /* trace launches of the last wavefront batch that found rays */
+    uint32_t tail_waves;        /* profile mode: waves of the last mrt_render_frames with fewer extension rays than half the path slots */
+    uint32_t reserved;
 } mrt_stats;
 
 /* Read-only view of a host scene container (arrays in the ABI layouts of mrt_abi.h). */
@@ -128,6 +132,19 @@ int mrt_set_scene(mrt_ctx* ctx,
                   const mrt_material* materials, uint32_t material_count,
                   const mrt_light_triangle* lights, uint32_t light_count);
 int mrt_set_scene_from(mrt_ctx* ctx, const mrt_scene* scene);
+/* The same in two halves, for several contexts (GPUs) in one process: the host half — validation, both SAH trees, the
+ * records repacked for 128-bit loads — runs once, the device half uploads to each ctx.  A prepared scene is read-only
+ * after creation: any number of threads may upload from it at the same time. */
+typedef struct mrt_prepared_scene mrt_prepared_scene;
+int  mrt_scene_prepare(const mrt_vertex* vertices, uint32_t vertex_count,
+                       const uint32_t* indices, uint32_t triangle_count,
+                       const mrt_triangle_reference* references,
+                       const mrt_material* materials, uint32_t material_count,
+                       const mrt_light_triangle* lights, uint32_t light_count,
+                       uint32_t bvh_max_leaf, uint32_t bvh_threads, mrt_prepared_scene** out);
+int  mrt_scene_prepare_from(const mrt_scene* scene, uint32_t bvh_threads, mrt_prepared_scene** out);
+int  mrt_set_prepared_scene(mrt_ctx* ctx, const mrt_prepared_scene* prepared);
+void mrt_prepared_scene_destroy(mrt_prepared_scene* prepared);
 
 /* -mtkView:drawableSizeWillChange: (Renderer.mm:640-657): (re)allocate Ray / LightSamplingRay /
  * Intersection / image for width x height rays, zero-fill, restart accumulation.  width/height are
@@ -198,6 +215,22 @@ int mrt_read_image(mrt_ctx* ctx, float* rgba);
 int mrt_scale_image(mrt_ctx* ctx, float scale);          /* rgb *= scale, alpha = 1 */
 int mrt_clear_image(mrt_ctx* ctx);
 int mrt_image_device_ptr(mrt_ctx* ctx, void** device_ptr, size_t* bytes); /* for NCCL reduce */
+
+/* ---- multi-GPU plumbing (no reference counterpart: one MTLCommandQueue on one device, Renderer.mm:153) -------------
+ * The library itself never talks to NCCL; the caller (host/mrt_render.c, bench.py) enqueues its collective on the
+ * ctx stream between these calls, so a step needs no host synchronisation.
+ *   sample sharding: MRT_ACCUM_SUM renders -> ncclAllReduce(image -> result) -> mrt_scale_buffer(result, 1/frames)
+ *   row sharding:    mrt_set_row_shard     -> mrt_pack_rows(send) -> ncclAllGather(send -> recv) -> mrt_unpack_rows(recv)
+ * mrt_stream_handle returns the ctx's cudaStream_t.  mrt_scale_buffer: rgb *= scale, alpha = 1 on any device buffer of
+ * `pixels` float4.  mrt_shard_layout: rows_max = ceil(H / shards) and the bytes one shard sends.  mrt_pack_rows copies
+ * the rows this ctx owns (mrt_set_row_shard) to a contiguous device buffer of rows_max * W float4; mrt_unpack_rows
+ * scatters `shards` such blocks (shard g at offset g * bytes_per_shard) back to rows g, g + shards, ... of the image —
+ * bit-identical to the single-device image, and the owned rows keep accumulating across steps. */
+int mrt_stream_handle(mrt_ctx* ctx, void** cuda_stream);
+int mrt_scale_buffer(mrt_ctx* ctx, void* device_rgba, size_t pixels, float scale);
+int mrt_shard_layout(mrt_ctx* ctx, uint32_t shards, uint32_t* rows_max, size_t* bytes_per_shard);
+int mrt_pack_rows(mrt_ctx* ctx, void* device_dst);
+int mrt_unpack_rows(mrt_ctx* ctx, const void* device_src, uint32_t shards);
 int mrt_read_buffer(mrt_ctx* ctx, uint32_t which, void* dst, size_t bytes);
 int mrt_write_buffer(mrt_ctx* ctx, uint32_t which, const void* src, size_t bytes);
 int mrt_get_stats(mrt_ctx* ctx, mrt_stats* out);

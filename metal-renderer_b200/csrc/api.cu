@@ -18,8 +18,14 @@
 #include "kernels.h"
 #include "mrt.h"
 #include "scene.h"
+#include <nvtx3/nvToolsExt.h>       // header-only; ranges carry the reference's encoder labels (Renderer.mm:505, 527, 557, 574)
 
 using namespace mrt;
+
+#ifndef MRT_WF_SORT_DEFAULT
+#define MRT_WF_SORT_DEFAULT 0       /* ray ordering grid bits per axis of the production build (MRT_WF_SORT overrides) */
+#endif
+struct NvtxRange { explicit NvtxRange(const char* name) { nvtxRangePushA(name); } ~NvtxRange() { nvtxRangePop(); } };
 
 static thread_local std::string g_last_error;
 static int fail(int code, const char* fmt, ...) {
@@ -70,6 +76,14 @@ struct mrt_ctx {
     unsigned int* dWaveCounts = nullptr; size_t waveCountCap = 0;   // per-wave queue sizes (profile mode)
     float4* dSamples = nullptr; size_t sampleCap = 0;            // per-sample radiance of a wavefront batch
     void* wfArena = nullptr;
+    float sceneLo[3] = {0, 0, 0}, sceneHi[3] = {1, 1, 1};        // bounding box of the scene's vertices (ray-ordering grid)
+    // wave loop as a CUDA graph: first shade -> WHILE { trace, shade, trace, shade } -> resolve; rebuilt when its kernel
+    // arguments change (another size, frame count, shard, accumulate mode ...), replayed otherwise
+    cudaGraphExec_t wfGraph = nullptr; std::string wfGraphKey;
+    cudaStream_t captureStream = nullptr;                        // body of the WHILE node is captured on this one
+    volatile unsigned int* hStop = nullptr; uint32_t batchSerial = 0;   // polling host loop: mapped word the trace kernel writes
+    cudaEvent_t pollEvents[4] = {};                              // polling host loop: one event every 8 waves
+    uint64_t graphKernels = 0; uint32_t kernelsPerWave = 2;      // kernels launched by graph replays (read back in mrt_get_stats)
     mrt_stats stats{};
 
     Grid2D grid() const { Grid2D g; g.W = W; g.H = H; g.rowFirst = rowFirst; g.rowStride = rowStride; return g; }
@@ -117,6 +131,27 @@ static int ensure_table(mrt_ctx* c, size_t entries) {
     return MRT_OK;
 }
 
+static int create_resources(mrt_ctx* c) {
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->captureStream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&c->ev0)); CK(cudaEventCreate(&c->ev1)); CK(cudaEventCreate(&c->evK0)); CK(cudaEventCreate(&c->evK1));
+    CK(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
+    for (int g = 0; g < 4; ++g) { CK(cudaStreamCreateWithFlags(&c->groupStream[g], cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&c->evJoin[g], cudaEventDisableTiming)); }
+    for (auto& e : c->user) CK(cudaEventCreate(&e));
+    for (auto& e : c->pollEvents) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&c->tableCopied, cudaEventDisableTiming));
+    CK(cudaMalloc(&c->dCounters, 4 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(c->dCounters, 0, 4 * sizeof(unsigned long long), c->stream));
+    CK(cudaMalloc(&c->dHead, sizeof(unsigned int)));
+    {   // mapped host word the trace kernel writes when a batch is over (polling host loop)
+        void* h = nullptr;
+        CK(cudaHostAlloc(&h, 64, cudaHostAllocMapped));
+        std::memset(h, 0, 64);
+        c->hStop = static_cast<volatile unsigned int*>(h);
+    }
+    return ensure_pool(c, MRT_NOISE_SLOTS + 16);
+}
+
 extern "C" {
 
 const char* mrt_last_error(void) { return g_last_error.c_str(); }
@@ -153,17 +188,8 @@ int mrt_create(const mrt_config* cfg, mrt_ctx** out) {
     NEED(c, MRT_E_NOMEM, "out of host memory");
     c->cfg = def;
     if (c->cfg.bvh_max_leaf == 0) c->cfg.bvh_max_leaf = 4;
-    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    CK(cudaEventCreate(&c->ev0)); CK(cudaEventCreate(&c->ev1)); CK(cudaEventCreate(&c->evK0)); CK(cudaEventCreate(&c->evK1));
-    CK(cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
-    for (int g = 0; g < 4; ++g) { CK(cudaStreamCreateWithFlags(&c->groupStream[g], cudaStreamNonBlocking)); CK(cudaEventCreateWithFlags(&c->evJoin[g], cudaEventDisableTiming)); }
-    for (auto& e : c->user) CK(cudaEventCreate(&e));
-    CK(cudaEventCreateWithFlags(&c->tableCopied, cudaEventDisableTiming));
-    CK(cudaMalloc(&c->dCounters, 4 * sizeof(unsigned long long)));
-    CK(cudaMemsetAsync(c->dCounters, 0, 4 * sizeof(unsigned long long), c->stream));
-    CK(cudaMalloc(&c->dHead, sizeof(unsigned int)));
-    int rc = ensure_pool(c, MRT_NOISE_SLOTS + 16);
-    if (rc) { delete c; return rc; }
+    int rc = create_resources(c);
+    if (rc != MRT_OK) { mrt_destroy(c); return rc; }       // a half-built context releases whatever it already holds
     *out = c;
     return MRT_OK;
 }
@@ -171,16 +197,21 @@ int mrt_create(const mrt_config* cfg, mrt_ctx** out) {
 int mrt_destroy(mrt_ctx* c) {
     if (!c) return MRT_OK;
     cudaSetDevice(c->cfg.device);
-    cudaStreamSynchronize(c->stream);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->wfGraph) cudaGraphExecDestroy(c->wfGraph);
     free_scene(c); free_sized(c);
     cudaFree(c->dNoisePool); cudaFree(c->dFrameTable); cudaFree(c->dCounters); cudaFree(c->dHead); cudaFree(c->dWaveCounts); cudaFree(c->dSamples);
     for (auto& e : c->profEvents) cudaEventDestroy(e);
     if (c->hFrameTable) cudaFreeHost(c->hFrameTable);
-    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->evK0); cudaEventDestroy(c->evK1); cudaEventDestroy(c->tableCopied);
-    for (auto& e : c->user) cudaEventDestroy(e);
+    for (cudaEvent_t e : {c->ev0, c->ev1, c->evK0, c->evK1, c->tableCopied}) if (e) cudaEventDestroy(e);
+    for (auto& e : c->user) if (e) cudaEventDestroy(e);
+    for (auto& e : c->pollEvents) if (e) cudaEventDestroy(e);
+    if (c->hStop) cudaFreeHost(const_cast<unsigned int*>(c->hStop));
+    if (c->captureStream) cudaStreamDestroy(c->captureStream);
     for (int g = 0; g < 4; ++g) { if (c->groupStream[g]) { cudaStreamSynchronize(c->groupStream[g]); cudaStreamDestroy(c->groupStream[g]); } if (c->evJoin[g]) cudaEventDestroy(c->evJoin[g]); }
     if (c->evFork) cudaEventDestroy(c->evFork);
-    cudaStreamDestroy(c->stream);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    cudaGetLastError();
     delete c;
     return MRT_OK;
 }
@@ -215,10 +246,22 @@ static cudaError_t set_l2_window(mrt_ctx* c, void* base, size_t bytes) {
     return e;
 }
 
-int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count, const uint32_t* indices, uint32_t triangle_count,
-                  const mrt_triangle_reference* references, const mrt_material* materials, uint32_t material_count,
-                  const mrt_light_triangle* lights, uint32_t light_count) {
-    NEED(c, MRT_E_INVALID, "ctx is NULL");
+// Host half of -initRaytracing (Renderer.mm:450-469): validation, both trees, records repacked for 128-bit loads.
+// Built once, uploaded to any number of contexts (one per GPU) by mrt_set_prepared_scene.
+struct mrt_prepared_scene {
+    BvhResult bvh; Bvh8Result bvh8;
+    std::vector<float> shade, mats, lts;
+    std::vector<uint32_t> cdfAndGuide, triSlotWide, triSlotBinary;
+    uint32_t cdfCount = 0, guideBuckets = 0, lightCount = 0, triangleCount = 0;
+    float lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
+};
+
+int mrt_scene_prepare(const mrt_vertex* vertices, uint32_t vertex_count, const uint32_t* indices, uint32_t triangle_count,
+                      const mrt_triangle_reference* references, const mrt_material* materials, uint32_t material_count,
+                      const mrt_light_triangle* lights, uint32_t light_count, uint32_t bvh_max_leaf, uint32_t bvh_threads,
+                      mrt_prepared_scene** out) {
+    NEED(out, MRT_E_INVALID, "out is NULL");
+    *out = nullptr;
     NEED(vertices && indices && references && materials && lights, MRT_E_INVALID, "mrt_set_scene: NULL array");
     NEED(triangle_count < (1u << 28), MRT_E_INVALID, "triangle_count must be < 2^28");
     for (size_t i = 0; i < 3 * (size_t)triangle_count; ++i)
@@ -230,28 +273,34 @@ int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count,
         NEED(r.lightTriangleIndex == MRT_NOT_A_LIGHT || r.lightTriangleIndex < light_count, MRT_E_INVALID, "reference %u: lightTriangleIndex out of range", t);
     }
     for (uint32_t l = 0; l < light_count; ++l) NEED(lights[l].index < triangle_count, MRT_E_INVALID, "light %u: index out of range", l);
-    CK(cudaSetDevice(c->cfg.device));
-    CK(cudaStreamSynchronize(c->stream));
-    free_scene(c);
-
-    BvhResult bvh;
-    build_bvh(vertices, indices, triangle_count, c->cfg.bvh_max_leaf, c->cfg.bvh_threads, bvh);
-    NEED(bvh.depth < MRT_STACK_DEPTH_HOST, MRT_E_INVALID, "BVH depth %u exceeds traversal stack", bvh.depth);
+    // selectLightTriangle (KernelHelpers.h:49-54) scans the cdf linearly; the kernels search it by bisection from a guide
+    // table, which selects the same light only if the cdf does not decrease (Renderer.mm:435-448 builds it that way)
+    for (uint32_t l = 0; l < light_count; ++l)
+        NEED(lights[l].cdf <= lights[l + 1].cdf, MRT_E_INVALID, "light cdf decreases at %u (%g > %g): build it as Renderer.mm:435-448 does", l,
+             (double)lights[l].cdf, (double)lights[l + 1].cdf);
+    mrt_prepared_scene* P = new (std::nothrow) mrt_prepared_scene();
+    NEED(P, MRT_E_NOMEM, "out of host memory");
+    if (bvh_max_leaf == 0) bvh_max_leaf = 4;
+    build_bvh(vertices, indices, triangle_count, bvh_max_leaf, bvh_threads, P->bvh);
+    if (!(P->bvh.depth < MRT_STACK_DEPTH_HOST)) { const uint32_t d = P->bvh.depth; delete P; return fail(MRT_E_INVALID, "BVH depth %u exceeds traversal stack", d); }
+    build_bvh8(vertices, indices, triangle_count, bvh_threads, P->bvh8);
+    if (!(P->bvh8.depth + 2 < 32)) { const uint32_t d = P->bvh8.depth; delete P; return fail(MRT_E_INVALID, "wide BVH depth %u exceeds traversal stack", d); }
 
     // shading records: vertices gathered per triangle through TriangleReference.tri (Shaders.metal:129,140)
-    std::vector<float> shade(20 * (size_t)std::max(1u, triangle_count), 0.0f);
+    P->shade.assign(20 * (size_t)std::max(1u, triangle_count), 0.0f);
     for (uint32_t t = 0; t < triangle_count; ++t) {
-        float* s = &shade[20 * (size_t)t];
+        float* s = &P->shade[20 * (size_t)t];
         const mrt_triangle_reference& r = references[t];
         for (int k = 0; k < 3; ++k) { std::memcpy(s + 3 * k, vertices[r.tri[k]].v, 12); std::memcpy(s + 9 + 3 * k, vertices[r.tri[k]].n, 12); }
         std::memcpy(s + 18, &r.materialIndex, 4); std::memcpy(s + 19, &r.lightTriangleIndex, 4);
     }
-    std::vector<float> mats(8 * (size_t)std::max(1u, material_count), 0.0f);
-    for (uint32_t m = 0; m < material_count; ++m) std::memcpy(&mats[8 * (size_t)m], &materials[m], 32);
-    std::vector<float> lts(24 * (size_t)(light_count + 1), 0.0f), cdf(light_count + 1);
+    P->mats.assign(8 * (size_t)std::max(1u, material_count), 0.0f);
+    for (uint32_t m = 0; m < material_count; ++m) std::memcpy(&P->mats[8 * (size_t)m], &materials[m], 32);
+    P->lts.assign(24 * (size_t)(light_count + 1), 0.0f);
+    std::vector<float> cdf(light_count + 1);
     for (uint32_t l = 0; l <= light_count; ++l) {
         const mrt_light_triangle& L = lights[l];
-        float* p = &lts[24 * (size_t)l];
+        float* p = &P->lts[24 * (size_t)l];
         std::memcpy(p, L.emissive.values, 12); p[3] = L.area;
         std::memcpy(p + 4, L.v1.v, 12); p[7] = L.pdf;
         std::memcpy(p + 8, L.v1.n, 12); std::memcpy(p + 11, &L.index, 4);
@@ -259,16 +308,6 @@ int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count,
         std::memcpy(p + 18, L.v3.v, 12); std::memcpy(p + 21, L.v3.n, 12);
         cdf[l] = L.cdf;
     }
-    auto upload = [&](void** dst, const void* src, size_t bytes) -> cudaError_t {
-        cudaError_t e = cudaMalloc(dst, std::max<size_t>(bytes, 16));
-        if (e != cudaSuccess) return e;
-        return bytes ? cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice) : cudaSuccess;
-    };
-    CK(upload(&c->dNodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(BvhNode)));
-    CK(upload(&c->dTris, bvh.tris.data(), bvh.tris.size() * sizeof(BvhTri)));
-    CK(upload(&c->dShade, shade.data(), shade.size() * 4));
-    CK(upload(&c->dMats, mats.data(), mats.size() * 4));
-    CK(upload(&c->dLights, lts.data(), lts.size() * 4));
     // guide table for selectLightTriangle (device_shading.cuh): the exact host search at the start of every slice
     uint32_t buckets = 0;
     std::vector<uint32_t> guide;
@@ -279,15 +318,46 @@ int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count,
         for (uint32_t b = 0; b < buckets; ++b) guide[b] = select(float(b) / float(buckets));
         guide[buckets] = light_count;
     }
-    std::vector<uint32_t> cdfAndGuide(cdf.size() + guide.size());
-    std::memcpy(cdfAndGuide.data(), cdf.data(), cdf.size() * 4);
-    if (!guide.empty()) std::memcpy(cdfAndGuide.data() + cdf.size(), guide.data(), guide.size() * 4);
-    CK(upload(&c->dCdf, cdfAndGuide.data(), cdfAndGuide.size() * 4));
-    c->S.lightGuide = buckets ? reinterpret_cast<const uint32_t*>(c->dCdf) + cdf.size() : nullptr;
-    c->S.lightGuideBuckets = buckets;
-    Bvh8Result bvh8;
-    build_bvh8(vertices, indices, triangle_count, c->cfg.bvh_threads, bvh8);
-    NEED(bvh8.depth + 2 < 32, MRT_E_INVALID, "wide BVH depth %u exceeds traversal stack", bvh8.depth);
+    P->cdfAndGuide.resize(cdf.size() + guide.size());
+    std::memcpy(P->cdfAndGuide.data(), cdf.data(), cdf.size() * 4);
+    if (!guide.empty()) std::memcpy(P->cdfAndGuide.data() + cdf.size(), guide.data(), guide.size() * 4);
+    P->cdfCount = (uint32_t)cdf.size(); P->guideBuckets = buckets;
+    P->triSlotWide.assign(std::max(1u, triangle_count), 0u);
+    for (size_t k = 0; k < P->bvh8.tris.size(); ++k) P->triSlotWide[P->bvh8.tris[k].index] = (uint32_t)k;
+    P->triSlotBinary.assign(std::max(1u, triangle_count), 0u);
+    for (size_t k = 0; k < P->bvh.tris.size(); ++k) P->triSlotBinary[P->bvh.tris[k].index] = (uint32_t)k;
+    P->lightCount = light_count; P->triangleCount = triangle_count;
+    if (vertex_count) {
+        for (int a = 0; a < 3; ++a) { P->lo[a] = INFINITY; P->hi[a] = -INFINITY; }
+        for (uint32_t v = 0; v < vertex_count; ++v)
+            for (int a = 0; a < 3; ++a) { const float x = vertices[v].v[a]; P->lo[a] = std::min(P->lo[a], x); P->hi[a] = std::max(P->hi[a], x); }
+    }
+    *out = P;
+    return MRT_OK;
+}
+void mrt_prepared_scene_destroy(mrt_prepared_scene* p) { delete p; }
+
+// Device half: upload to THIS context.  The prepared scene is only read, so several contexts (threads) may share it.
+int mrt_set_prepared_scene(mrt_ctx* c, const mrt_prepared_scene* P) {
+    NEED(c && P, MRT_E_INVALID, "NULL argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    free_scene(c);
+    if (c->wfGraph) { cudaGraphExecDestroy(c->wfGraph); c->wfGraph = nullptr; c->wfGraphKey.clear(); }
+    const BvhResult& bvh = P->bvh; const Bvh8Result& bvh8 = P->bvh8;
+    auto upload = [&](void** dst, const void* src, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(dst, std::max<size_t>(bytes, 16));
+        if (e != cudaSuccess) return e;
+        return bytes ? cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice) : cudaSuccess;
+    };
+    CK(upload(&c->dNodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(BvhNode)));
+    CK(upload(&c->dTris, bvh.tris.data(), bvh.tris.size() * sizeof(BvhTri)));
+    CK(upload(&c->dShade, P->shade.data(), P->shade.size() * 4));
+    CK(upload(&c->dMats, P->mats.data(), P->mats.size() * 4));
+    CK(upload(&c->dLights, P->lts.data(), P->lts.size() * 4));
+    CK(upload(&c->dCdf, P->cdfAndGuide.data(), P->cdfAndGuide.size() * 4));
+    c->S.lightGuide = P->guideBuckets ? reinterpret_cast<const uint32_t*>(c->dCdf) + P->cdfCount : nullptr;
+    c->S.lightGuideBuckets = P->guideBuckets;
     {   // wide nodes and their triangle records share ONE allocation (nodes first), so that a single L2 access-policy
         // window can cover what the trace kernel gathers from
         const size_t nodeBytes = (bvh8.nodes.size() * sizeof(Bvh8Node) + 255) & ~size_t(255);
@@ -300,20 +370,40 @@ int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count,
     }
     c->S.nodes8 = (const float4*)c->dNodes8; c->S.tris8 = (const float4*)c->dTris8;
     const bool wide = trace_uses_wide_bvh();
-    const std::vector<BvhTri>& order = wide ? bvh8.tris : bvh.tris;
-    std::vector<uint32_t> triSlot(std::max(1u, triangle_count), 0u);
-    for (size_t k = 0; k < order.size(); ++k) triSlot[order[k].index] = (uint32_t)k;
+    const std::vector<uint32_t>& triSlot = wide ? P->triSlotWide : P->triSlotBinary;
     CK(upload(&c->dTriSlot, triSlot.data(), triSlot.size() * 4));
     c->wf.triSlot = (const uint32_t*)c->dTriSlot;
     c->wf.triRecords = (const float4*)(wide ? c->dTris8 : c->dTris);
     c->stats.bvh8_nodes = (uint32_t)bvh8.nodes.size(); c->stats.bvh8_depth = bvh8.depth;
     c->S.nodes = (const float4*)c->dNodes; c->S.tris = (const float4*)c->dTris; c->S.shadeTris = (const float4*)c->dShade;
     c->S.materials = (const float4*)c->dMats; c->S.lights = (const float4*)c->dLights; c->S.lightCdf = (const float*)c->dCdf;
-    c->S.lightCount = light_count; c->S.triangleCount = triangle_count;
+    c->S.lightCount = P->lightCount; c->S.triangleCount = P->triangleCount;
     c->stats.bvh_nodes = (uint32_t)bvh.nodes.size(); c->stats.bvh_depth = bvh.depth; c->stats.bvh_sah_cost = bvh.sah_cost;
     c->stats.bvh_build_ms = (float)bvh.build_ms;
+    c->stats.bvh8_build_ms = (float)bvh8.build_ms;
+    for (int a = 0; a < 3; ++a) { c->sceneLo[a] = P->lo[a]; c->sceneHi[a] = P->hi[a]; }
     c->haveScene = true;
     return MRT_OK;
+}
+
+int mrt_set_scene(mrt_ctx* c, const mrt_vertex* vertices, uint32_t vertex_count, const uint32_t* indices, uint32_t triangle_count,
+                  const mrt_triangle_reference* references, const mrt_material* materials, uint32_t material_count,
+                  const mrt_light_triangle* lights, uint32_t light_count) {
+    NEED(c, MRT_E_INVALID, "ctx is NULL");
+    mrt_prepared_scene* P = nullptr;
+    int rc = mrt_scene_prepare(vertices, vertex_count, indices, triangle_count, references, materials, material_count, lights, light_count,
+                               c->cfg.bvh_max_leaf, c->cfg.bvh_threads, &P);
+    if (rc != MRT_OK) return rc;
+    rc = mrt_set_prepared_scene(c, P);
+    delete P;
+    return rc;
+}
+
+int mrt_scene_prepare_from(const mrt_scene* s, uint32_t bvh_threads, mrt_prepared_scene** out) {
+    NEED(s && out, MRT_E_INVALID, "NULL argument");
+    return mrt_scene_prepare(s->vertices.data(), (uint32_t)s->vertices.size(), s->indices.data(), (uint32_t)s->references.size(),
+                             s->references.data(), s->materials.data(), (uint32_t)s->materials.size(), s->lights.data(), s->light_count,
+                             4, bvh_threads, out);
 }
 
 int mrt_set_scene_from(mrt_ctx* c, const mrt_scene* s) {
@@ -339,14 +429,21 @@ int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
     CK(cudaMemsetAsync(c->dIsects, 0, n * sizeof(mrt_intersection), c->stream));
     CK(cudaMemsetAsync(c->dImage, 0, n * sizeof(float4), c->stream));
     c->W = width; c->H = height;
+    if (c->wfGraph) { cudaGraphExecDestroy(c->wfGraph); c->wfGraph = nullptr; c->wfGraphKey.clear(); }
     {   // wavefront path state: one slot per pixel of an 8x4-tiled grid, SoA float4 arrays + two queue pairs
         // MRT_WF_SLOTS: path slots per pixel (default 1).  More slots than pixels = fewer, larger waves.
+#ifdef MRT_EXPERIMENTS
         static const int slotMult = std::min(4, std::max(1, getenv("MRT_WF_SLOTS") ? atoi(getenv("MRT_WF_SLOTS")) : 1));
+#else
+        const int slotMult = 1;
+#endif
         c->wfSlotMult = (uint32_t)slotMult;
         const size_t slots = (size_t)((width + 7u) / 8u) * ((height + 3u) / 4u) * 32u * slotMult;
         const size_t f4 = slots * sizeof(float4), u4 = slots * sizeof(uint32_t);
         const size_t regions = slots / 32;                                  // smallest region = one 8x4 tile
-        const size_t total = 7 * f4 + 6 * u4 + 128 + 2 * regions * sizeof(uint32_t);      // 128 = 4 groups x (counts[4], heads[2], 2 spare)
+        const size_t histBytes = 4 * 4 * (size_t)wf_sort_buckets(3) * sizeof(uint32_t);   // up to 4 groups x (2 counts + 2 cursors) x 4096 buckets
+        const size_t ctlBytes = 128 + MRT_CTL_WORDS * sizeof(uint32_t) + 96;             // 128 = 4 groups x (counts[4], heads[2], 2 spare)
+        const size_t total = 7 * f4 + 10 * u4 + ctlBytes + histBytes + 2 * regions * sizeof(uint32_t);
         CK(cudaMalloc(&c->wfArena, total));
         CK(cudaMemsetAsync(c->wfArena, 0, total, c->stream));
         char* p = static_cast<char*>(c->wfArena);
@@ -356,7 +453,10 @@ int mrt_resize(mrt_ctx* c, uint32_t width, uint32_t height) {
         c->wf.S0 = take4(); c->wf.S1 = take4();
         c->wf.visible = takeU(); c->wf.item = takeU();
         c->wf.queueExt[0] = takeU(); c->wf.queueExt[1] = takeU(); c->wf.queueShadow[0] = takeU(); c->wf.queueShadow[1] = takeU();
+        for (int k = 0; k < 2; ++k) { c->wf.sortSlot[k] = takeU(); c->wf.sortKey[k] = takeU(); }
         c->wf.counts = reinterpret_cast<unsigned int*>(p); c->wf.heads = c->wf.counts + 4; p += 128;
+        c->wf.ctl = reinterpret_cast<unsigned int*>(p); p += MRT_CTL_WORDS * sizeof(uint32_t) + 96;
+        c->wf.sortHist = reinterpret_cast<unsigned int*>(p); p += histBytes;
         c->wf.regionNext = reinterpret_cast<unsigned int*>(p); c->wf.blockRegion = c->wf.regionNext + regions;
         c->wf.slots = (uint32_t)slots; c->wf.pixels = (uint32_t)slots;
     }
@@ -409,10 +509,227 @@ int mrt_set_pipeline(mrt_ctx* c, uint32_t pipeline) {
 
 static inline const float4* slot_tile(const mrt_ctx* c, uint32_t slot) { return c->dNoisePool + (slot % MRT_NOISE_SLOTS) * kTileFloat4; }
 
+
+// ---- the wavefront batch: work items (frame, pixel) handed to path slots dynamically, finished samples parked in a
+// per-sample buffer and folded into the image in frame order at the end.  The batch is cut into sub-batches so that the
+// sample buffer (16 B per sample) stays within a quarter of the free device memory.
+//
+// How the waves are issued:
+//   * default — ONE CUDA graph per sub-batch: first shade -> WHILE { trace, shade, trace, shade } -> resolve.  Block 0 of
+//     the trace kernel ends the loop (cudaGraphSetConditional) when nothing is queued and every sample of the batch has
+//     been parked, so no empty wave is launched and the host issues a single cudaGraphLaunch.  The instantiated graph is
+//     kept and replayed as long as the kernel arguments do not change.
+//   * profile mode (mrt_set_profile: a CUDA-event pair around every trace launch), MRT_WF_GRAPH=0 and the experiments
+//     build's slot groups — a host loop that runs at most 2 x 8 waves ahead of the device and stops when the trace kernel
+//     has written the batch's serial number to a mapped host word.
+// A loop that reaches the proven bound frames x L + L + 2 without finishing ends anyway; k_wf_resolve_samples then
+// leaves the failure word that check_drained reports.
+static int env_knob(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
+#ifdef MRT_EXPERIMENTS
+#define EXP_KNOB(name, dflt) env_knob(name, dflt)
+#else
+#define EXP_KNOB(name, dflt) (dflt)
+#endif
+
+static int build_wave_graph(mrt_ctx* c, const RenderParams& q, WfBuffers b, bool count, const std::string& key) {
+    if (c->wfGraph) { cudaGraphExecDestroy(c->wfGraph); c->wfGraph = nullptr; c->wfGraphKey.clear(); }
+    cudaGraph_t g = nullptr, body = nullptr, tmp = nullptr;
+    cudaGraphConditionalHandle handle = 0;
+    cudaError_t e = cudaGraphCreate(&g, 0);
+    bool capMain = false, capBody = false;
+    if (e == cudaSuccess) e = cudaGraphConditionalHandleCreate(&handle, g, 1, cudaGraphCondAssignDefault);
+    b.condHandle = (unsigned long long)handle; b.hostStop = nullptr; b.batchSerial = 0;
+    if (e == cudaSuccess) { e = cudaStreamBeginCaptureToGraph(c->stream, g, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed); capMain = e == cudaSuccess; }
+    if (e == cudaSuccess) {
+        launch_wf_shade(c->stream, q, b, 0, true, count);
+        launch_wf_sort(c->stream, b, 0);
+        e = cudaGetLastError();
+    }
+    cudaGraphNode_t loop = nullptr;
+    if (e == cudaSuccess) {
+        cudaStreamCaptureStatus st; const cudaGraphNode_t* deps = nullptr; size_t nDeps = 0;
+        e = cudaStreamGetCaptureInfo_v2(c->stream, &st, nullptr, nullptr, &deps, &nDeps);
+        cudaGraphNodeParams np = { cudaGraphNodeTypeConditional };
+        np.conditional.handle = handle; np.conditional.type = cudaGraphCondTypeWhile; np.conditional.size = 1;
+        if (e == cudaSuccess) e = cudaGraphAddNode(&loop, g, deps, nDeps, &np);
+        if (e == cudaSuccess) { body = np.conditional.phGraph_out[0]; e = cudaStreamUpdateCaptureDependencies(c->stream, &loop, 1, cudaStreamSetCaptureDependencies); }
+    }
+    if (e == cudaSuccess) { e = cudaStreamBeginCaptureToGraph(c->captureStream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed); capBody = e == cudaSuccess; }
+    if (e == cudaSuccess) {
+        for (uint32_t w = 0; w < 2u; ++w) {
+            launch_wf_trace(c->captureStream, q, b, w, c->countVisits);
+            launch_wf_shade(c->captureStream, q, b, w, false, count);
+            launch_wf_sort(c->captureStream, b, (w + 1u) & 1u);
+        }
+        e = cudaGetLastError();
+    }
+    if (capBody) { cudaError_t e2 = cudaStreamEndCapture(c->captureStream, &tmp); if (e == cudaSuccess) e = e2; }
+    if (e == cudaSuccess) { launch_wf_resolve_samples(c->stream, q, b); e = cudaGetLastError(); }
+    if (capMain) { cudaError_t e2 = cudaStreamEndCapture(c->stream, &tmp); if (e == cudaSuccess) e = e2; }
+    if (e == cudaSuccess) e = cudaGraphInstantiate(&c->wfGraph, g, 0);
+    if (g) cudaGraphDestroy(g);
+    if (e != cudaSuccess) {
+        c->wfGraph = nullptr;
+        cudaGetLastError();
+        return fail(MRT_E_CUDA, "building the wave graph failed: %s", cudaGetErrorString(e));
+    }
+    c->wfGraphKey = key;
+    return MRT_OK;
+}
+
+static int render_wavefront(mrt_ctx* c, const RenderParams& p, uint32_t n_frames) {
+    WfBuffers b = c->wf;
+    b.waveLog = nullptr;
+    b.pixels = ((c->W + 7u) / 8u) * ((p.ownedRows + 3u) / 4u) * 32u;
+    b.slots = b.pixels * c->wfSlotMult;
+    const bool count = c->cfg.count_rays != 0;
+    size_t freeB = 0, totalB = 0;
+    CK(cudaMemGetInfo(&freeB, &totalB));
+    const size_t perFrame = (size_t)std::max(1u, b.pixels) * sizeof(float4);
+    const size_t budget = std::max(perFrame, std::min<size_t>((freeB + c->sampleCap) / 4, (size_t)24 << 30));
+    const uint32_t maxSub = (uint32_t)std::max<size_t>(1, std::min<size_t>(budget / perFrame, n_frames));
+    if (c->sampleCap < (size_t)maxSub * perFrame) {
+        CK(cudaStreamSynchronize(c->stream));
+        cudaFree(c->dSamples); c->dSamples = nullptr; c->sampleCap = 0;
+        CK(cudaMalloc(&c->dSamples, (size_t)maxSub * perFrame));
+        c->sampleCap = (size_t)maxSub * perFrame;
+    }
+    b.samples = c->dSamples;
+    c->profUsed = 0;
+    // ray ordering (MRT_WF_SORT = grid bits per axis, 0 = off; MRT_WF_SORT_MODE bit 0 = octant-major keys)
+    static const int sortBits = std::min(3, std::max(0, env_knob("MRT_WF_SORT", MRT_WF_SORT_DEFAULT)));
+    static const int sortMode = env_knob("MRT_WF_SORT_MODE", 0);
+    b.sortBits = (uint32_t)sortBits; b.sortMode = (uint32_t)sortMode;
+    for (int a = 0; a < 3; ++a) {
+        const float ext = std::max(c->sceneHi[a] - c->sceneLo[a], 1e-20f);
+        b.sortLo[a] = c->sceneLo[a]; b.sortScale[a] = float(1u << b.sortBits) / ext;
+    }
+    // waves per sub-batch of nf frames: greedy assignment finishes within (total segments / slots) + L waves, plus
+    // one wave per padding pixel a slot may draw
+    const uint32_t Lp = c->cfg.max_path_length;
+    // MRT_WF_MAX_WAVES (tests only): cut the schedule short to exercise the failure flag of check_drained
+    static const long long waveCap = getenv("MRT_WF_MAX_WAVES") ? atoll(getenv("MRT_WF_MAX_WAVES")) : 0;
+    auto waves_for = [Lp](uint32_t nf) {
+        const uint64_t bound = (uint64_t)nf * Lp + Lp + 2;
+        return waveCap > 0 ? std::min<uint64_t>(bound, (uint64_t)waveCap) : bound;
+    };
+    uint64_t wavesTotal = 0;
+    for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) wavesTotal += 4 * waves_for(std::min(maxSub, n_frames - f0));   // x4: up to 4 slot groups
+    if (c->profile) {
+        while (c->profEvents.size() < 2 * wavesTotal) { cudaEvent_t e; CK(cudaEventCreate(&e)); c->profEvents.push_back(e); }
+        if (c->waveCountCap < wavesTotal) {
+            cudaFree(c->dWaveCounts); c->dWaveCounts = nullptr; c->waveCountCap = 0;
+            CK(cudaMalloc(&c->dWaveCounts, wavesTotal * 2 * sizeof(unsigned int)));
+            c->waveCountCap = wavesTotal;
+        }
+    }
+    // Slot groups (experiments build, MRT_WF_SPLIT=2..4): the slots are cut into equal parts, each with its own queues and
+    // stream, so that one group's kernels could fill the SMs freed while another group's persistent trace kernel drains.
+    // Measured on B200 (profiles/r1_k_sweep.log): 2 groups = no change, 3-4 groups 4-8 % slower; with the 64-register
+    // shade kernel 2 groups gain 1-2.6 %.  The production path runs one group on one stream.
+    static const int splitEnv = EXP_KNOB("MRT_WF_SPLIT", 1);
+    uint32_t groups = (uint32_t)std::min(4, std::max(1, splitEnv));
+    while (groups > 1 && b.slots / groups < 262144u) --groups;                     // small images: not worth splitting
+    uint32_t per = ((b.slots + groups - 1u) / groups + 255u) / 256u * 256u;
+    static const int graphEnv = env_knob("MRT_WF_GRAPH", 1);
+    const bool useGraph = graphEnv != 0 && !c->profile && groups == 1;
+    const uint32_t perWave = 2u + (b.sortBits ? 1u : 0u);                            // kernels per wave: trace, shade (, sort)
+    uint64_t launched = 0, pw = 0;
+    c->kernelsPerWave = perWave;
+    for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) {
+        const uint32_t nf = std::min(maxSub, n_frames - f0);
+        RenderParams q = p;
+        q.frames = c->dFrameTable + f0; q.nFrames = nf;
+        {   // MRT_WF_REGION (experiments build): 32 = per-tile counters claimed per warp (default), 256 = per shade block, 0 = one global counter
+            static const int rsEnv = EXP_KNOB("MRT_WF_REGION", 32);
+            b.regionSize = rsEnv == 32 ? 32u : (rsEnv <= 0 ? std::max(1u, b.pixels) : (uint32_t)((rsEnv + 255) / 256 * 256));
+            b.regions = (b.pixels + b.regionSize - 1u) / b.regionSize;
+        }
+        const uint64_t waves = waves_for(nf);
+        b.expected = c->W * p.ownedRows * nf;
+        b.waveLimit = (uint32_t)std::min<uint64_t>(waves, 0xFFFFFFFFull);
+        b.condHandle = 0; b.hostStop = nullptr; b.batchSerial = 0;
+        b.allCounts = b.counts; b.groups = groups; b.slotBase = 0;
+        // per group: counts[4], heads[2]; word 7 of group 0 is the failure word (check_drained reports and clears it)
+        CK(cudaMemsetAsync(b.counts, 0, 7 * sizeof(unsigned int), c->stream));
+        CK(cudaMemsetAsync(b.counts + 8, 0, 24 * sizeof(unsigned int), c->stream));
+        CK(cudaMemsetAsync(b.ctl, 0, MRT_CTL_BATCH_WORDS * sizeof(unsigned int), c->stream));
+        CK(cudaMemsetAsync(b.regionNext, 0, (size_t)b.regions * sizeof(unsigned int), c->stream));
+        if (b.sortBits) CK(cudaMemsetAsync(b.sortHist, 0, 4 * (size_t)wf_sort_buckets(b.sortBits) * sizeof(unsigned int), c->stream));
+        if (useGraph) {
+            std::string key(sizeof q + sizeof b + 2, '\0');
+            std::memcpy(&key[0], &q, sizeof q); std::memcpy(&key[sizeof q], &b, sizeof b);
+            key[sizeof q + sizeof b] = count ? 1 : 0; key[sizeof q + sizeof b + 1] = c->countVisits ? 1 : 0;
+            if (!c->wfGraph || key != c->wfGraphKey) { int rc = build_wave_graph(c, q, b, count, key); if (rc != MRT_OK) return rc; }
+            CK(cudaGraphLaunch(c->wfGraph, c->stream));
+            launched += 2 + (b.sortBits ? 1 : 0);                                 // first shade (+ sort), resolve; the waves are counted on the device
+            continue;
+        }
+        WfBuffers gb[4];
+        for (uint32_t g = 0; g < groups; ++g) {
+            const uint32_t at = std::min(b.slots, g * per), n = std::min(per, b.slots - at);
+            WfBuffers h = b;
+            h.P0 += at; h.P1 += at; h.P2 += at; h.P3 += at; h.H += at; h.S0 += at; h.S1 += at; h.visible += at; h.item += at;
+            for (int k = 0; k < 2; ++k) { h.queueExt[k] += at; h.queueShadow[k] += at; h.sortSlot[k] += at; h.sortKey[k] += at; }
+            h.sortHist = b.sortHist + (size_t)g * 4 * wf_sort_buckets(b.sortBits);
+            h.counts = b.counts + 8 * g; h.heads = h.counts + 4;
+            h.slots = n; h.slotBase = at;
+            gb[g] = h;
+        }
+        const bool poll = groups == 1;
+        const uint32_t serial = ++c->batchSerial;
+        if (poll) { gb[0].hostStop = c->hStop; gb[0].batchSerial = serial; }
+        auto stream_of = [&](uint32_t g) { return (c->profile || groups == 1) ? c->stream : c->groupStream[g]; };
+        const bool forked = stream_of(0) != c->stream;
+        if (forked) {
+            CK(cudaEventRecord(c->evFork, c->stream));
+            for (uint32_t g = 0; g < groups; ++g) CK(cudaStreamWaitEvent(c->groupStream[g], c->evFork, 0));
+        }
+        for (uint32_t g = 0; g < groups; ++g) { launch_wf_shade(stream_of(g), q, gb[g], 0, true, count); launch_wf_sort(stream_of(g), gb[g], 0); }
+        launched += groups * (perWave - 1u);
+        const uint32_t K = 8;                                                     // poll every K waves, run at most 2K waves ahead
+        for (uint64_t w = 0; w < waves; ++w) {
+            if (poll && w % K == 0) {
+                if (w >= 2 * K) {
+                    CK(cudaEventSynchronize(c->pollEvents[(w / K - 2) % 4]));
+                    if (*c->hStop == serial) break;
+                }
+                CK(cudaEventRecord(c->pollEvents[(w / K) % 4], c->stream));
+            }
+            for (uint32_t g = 0; g < groups; ++g, ++pw) {
+                cudaStream_t st = stream_of(g);
+                gb[g].waveLog = nullptr;
+                if (c->profile) {
+                    gb[g].waveLog = c->dWaveCounts + 2 * pw;        // the trace kernel notes its queue sizes there
+                    CK(cudaEventRecord(c->profEvents[2 * pw], st));
+                }
+                launch_wf_trace(st, q, gb[g], (uint32_t)(w & 1u), c->countVisits);
+                if (c->profile) CK(cudaEventRecord(c->profEvents[2 * pw + 1], st));
+                launch_wf_shade(st, q, gb[g], (uint32_t)w, false, count);
+                launch_wf_sort(st, gb[g], (uint32_t)((w + 1u) & 1u));
+                launched += perWave;
+            }
+        }
+        if (forked) {
+            for (uint32_t g = 0; g < groups; ++g) {
+                CK(cudaEventRecord(c->evJoin[g], c->groupStream[g]));
+                CK(cudaStreamWaitEvent(c->stream, c->evJoin[g], 0));
+            }
+        }
+        launch_wf_resolve_samples(c->stream, q, b);
+        launched += 1;
+    }
+    if (c->profile) c->profUsed = 2 * pw;
+    c->stats.kernel_launches += launched;
+    CK(cudaGetLastError());
+    return MRT_OK;
+}
+
 extern "C" {
 
 int mrt_raygen(mrt_ctx* c, uint32_t frame_index) {
     NEED_READY(c);
+    NvtxRange range("Ray generator");
     launch_raygen(c->stream, c->dRays, slot_tile(c, frame_index), c->grid());               // Renderer.mm:508-512
     LAUNCHED(c, 1);
     return MRT_OK;
@@ -424,6 +741,7 @@ int mrt_intersect(mrt_ctx* c, uint32_t which) {
     const void* rays = which == MRT_BUF_RAYS ? (const void*)c->dRays : (const void*)c->dLightRays;
     uint32_t stride = which == MRT_BUF_RAYS ? sizeof(mrt_ray) : sizeof(mrt_light_sampling_ray);  // setRayStride, Renderer.mm:519,545
     unsigned long long* live = c->cfg.count_rays ? c->dCounters + (which == MRT_BUF_RAYS ? 0 : 1) : nullptr;
+    NvtxRange range(which == MRT_BUF_RAYS ? "Intersect rays" : "Intersect light-sampling rays");
     CK(cudaMemsetAsync(c->dHead, 0, sizeof(unsigned int), c->stream));
     launch_intersect_persistent(c->stream, c->S, rays, stride, c->W * c->H, c->dIsects, c->grid(), true, live, c->dHead);
     LAUNCHED(c, 1);
@@ -432,6 +750,7 @@ int mrt_intersect(mrt_ctx* c, uint32_t which) {
 
 int mrt_shade(mrt_ctx* c, uint32_t frame_index, uint32_t bounce_iteration) {
     NEED_READY(c);
+    NvtxRange range("Intersection handler");
     launch_shade(c->stream, c->S, c->dIsects, c->dRays, c->dLightRays, slot_tile(c, frame_index + bounce_iteration),  // Renderer.mm:538
                  frame_index, c->cfg.max_path_length, c->grid());
     LAUNCHED(c, 1);
@@ -440,6 +759,7 @@ int mrt_shade(mrt_ctx* c, uint32_t frame_index, uint32_t bounce_iteration) {
 
 int mrt_shadow_resolve(mrt_ctx* c) {
     NEED_READY(c);
+    NvtxRange range("Light sampling");
     launch_shadow_resolve(c->stream, c->dIsects, c->dRays, c->dLightRays, c->grid());
     LAUNCHED(c, 1);
     return MRT_OK;
@@ -447,6 +767,7 @@ int mrt_shadow_resolve(mrt_ctx* c) {
 
 int mrt_accumulate(mrt_ctx* c, uint32_t frame_index) {
     NEED_READY(c);
+    NvtxRange range("Final image accumulation");
     launch_accumulate(c->stream, c->dImage, c->dRays, frame_index, c->cfg.accumulate_mode, c->grid());
     LAUNCHED(c, 1);
     c->nextFrame = frame_index + 1;
@@ -470,6 +791,7 @@ int mrt_render_frame_staged(mrt_ctx* c, uint32_t frame_index) {
 int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint32_t frame_stride, const float* noise_tiles) {
     NEED_READY(c);
     if (n_frames == 0) return MRT_OK;
+    NvtxRange range("performRaytracing (batch)");
     if (frame_stride == 0) frame_stride = 1;
     NEED((uint64_t)first_frame + (uint64_t)(n_frames - 1) * frame_stride < 0xFFFFFFFFull, MRT_E_INVALID, "frame index overflow");
     const uint32_t span = (n_frames - 1) * frame_stride + 1;              // tiles supplied: one per frame first..last
@@ -502,6 +824,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
         CK(cudaMemcpyAsync(c->dFrameTable, c->hFrameTable, n_frames * sizeof(FrameEntry), cudaMemcpyHostToDevice, c->stream));
         CK(cudaEventRecord(c->tableCopied, c->stream));
         RenderParams p;
+        std::memset(&p, 0, sizeof p);                                     // padding too: the wave graph is keyed on these bytes
         p.S = c->S; p.noisePool = c->dNoisePool; p.frames = c->dFrameTable; p.nFrames = n_frames; p.image = c->dImage;
         p.g = c->grid(); p.ownedRows = c->ownedRows(); p.maxPathLength = c->cfg.max_path_length; p.accumMode = c->cfg.accumulate_mode;
         p.counters = c->cfg.count_rays ? c->dCounters : nullptr;
@@ -511,113 +834,9 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
             launch_render_fused(c->stream, p, c->cfg.count_rays != 0);
             LAUNCHED(c, 1);
         } else {
-            // queue-compacted wavefront.  Work items (frame, pixel) are handed to path slots dynamically; finished samples
-            // go to a per-sample buffer and are folded into the image in frame order at the end.  The batch is cut into
-            // sub-batches so that the sample buffer (16 B per sample) stays within a quarter of the free device memory.
-            WfBuffers b = c->wf;
-            b.waveLog = nullptr;
-            b.pixels = ((c->W + 7u) / 8u) * ((p.ownedRows + 3u) / 4u) * 32u;
-            b.slots = b.pixels * c->wfSlotMult;
-            const bool count = c->cfg.count_rays != 0;
-            size_t freeB = 0, totalB = 0;
-            CK(cudaMemGetInfo(&freeB, &totalB));
-            const size_t perFrame = (size_t)std::max(1u, b.pixels) * sizeof(float4);
-            const size_t budget = std::max(perFrame, std::min<size_t>((freeB + c->sampleCap) / 4, (size_t)24 << 30));
-            const uint32_t maxSub = (uint32_t)std::max<size_t>(1, std::min<size_t>(budget / perFrame, n_frames));
-            if (c->sampleCap < (size_t)maxSub * perFrame) {
-                CK(cudaStreamSynchronize(c->stream));
-                cudaFree(c->dSamples); c->dSamples = nullptr; c->sampleCap = 0;
-                CK(cudaMalloc(&c->dSamples, (size_t)maxSub * perFrame));
-                c->sampleCap = (size_t)maxSub * perFrame;
-            }
-            b.samples = c->dSamples;
-            c->profUsed = 0;
-            // waves per sub-batch of nf frames: greedy assignment finishes within (total segments / slots) + L waves, plus
-            // one wave per padding pixel a slot may draw; waves that find both queues empty return at once
-            const uint32_t Lp = c->cfg.max_path_length;
-            // MRT_WF_MAX_WAVES (tests only): cut the schedule short to exercise the failure flag of check_drained
-            static const long long waveCap = getenv("MRT_WF_MAX_WAVES") ? atoll(getenv("MRT_WF_MAX_WAVES")) : 0;
-            auto waves_for = [Lp](uint32_t nf) {
-                const uint64_t bound = (uint64_t)nf * Lp + Lp + 2;
-                return waveCap > 0 ? std::min<uint64_t>(bound, (uint64_t)waveCap) : bound;
-            };
-            uint64_t wavesTotal = 0;
-            for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) wavesTotal += 4 * waves_for(std::min(maxSub, n_frames - f0));   // x4: up to 4 slot groups
-            if (c->profile) {
-                while (c->profEvents.size() < 2 * wavesTotal) { cudaEvent_t e; CK(cudaEventCreate(&e)); c->profEvents.push_back(e); }
-                if (c->waveCountCap < wavesTotal) {
-                    cudaFree(c->dWaveCounts); c->dWaveCounts = nullptr; c->waveCountCap = 0;
-                    CK(cudaMalloc(&c->dWaveCounts, wavesTotal * 2 * sizeof(unsigned int)));
-                    c->waveCountCap = wavesTotal;
-                }
-            }
-            // Slot groups (experiment, MRT_WF_SPLIT=2..4; default 1 = off): the slots are cut into equal parts, each with its
-            // own queues and stream, so that one group's kernels could fill the SMs freed while another group's persistent
-            // trace kernel drains.  Measured on B200 (profiles/r1_k_sweep.log): 2 groups = no change, 3-4 groups 4-8 %
-            // slower; with the 64-register shade kernel 2 groups gain 1-2.6 %.  The production path runs
-            // one group on one stream, which keeps the per-launch event timing of the trace kernel exact.
-            static const int splitEnv = getenv("MRT_WF_SPLIT") ? atoi(getenv("MRT_WF_SPLIT")) : 1;
-            uint32_t groups = (uint32_t)std::min(4, std::max(1, splitEnv));
-            while (groups > 1 && b.slots / groups < 262144u) --groups;                     // small images: not worth splitting
-            uint32_t per = ((b.slots + groups - 1u) / groups + 255u) / 256u * 256u;
-            WfBuffers gb[4];
-            for (uint32_t g = 0; g < groups; ++g) {
-                const uint32_t at = std::min(b.slots, g * per), n = std::min(per, b.slots - at);
-                WfBuffers h = b;
-                h.P0 += at; h.P1 += at; h.P2 += at; h.P3 += at; h.H += at; h.S0 += at; h.S1 += at; h.visible += at; h.item += at;
-                for (int q = 0; q < 2; ++q) { h.queueExt[q] += at; h.queueShadow[q] += at; }
-                h.counts = b.counts + 8 * g; h.heads = h.counts + 4;
-                h.slots = n; h.slotBase = at; h.allCounts = b.counts; h.groups = groups;
-                gb[g] = h;
-            }
-            b.allCounts = b.counts; b.groups = groups;
-            auto stream_of = [&](uint32_t g) { return (c->profile || groups == 1) ? c->stream : c->groupStream[g]; };
-            uint64_t launched = 0, pw = 0;
-            for (uint32_t f0 = 0; f0 < n_frames; f0 += maxSub) {
-                const uint32_t nf = std::min(maxSub, n_frames - f0);
-                RenderParams q = p;
-                q.frames = c->dFrameTable + f0; q.nFrames = nf;
-                {   // MRT_WF_REGION: 32 = per-tile counters claimed per warp (default), 256 = per shade block, 0 = one global counter
-                    static const int rsEnv = getenv("MRT_WF_REGION") ? atoi(getenv("MRT_WF_REGION")) : 32;
-                    b.regionSize = rsEnv == 32 ? 32u : (rsEnv <= 0 ? std::max(1u, b.pixels) : (uint32_t)((rsEnv + 255) / 256 * 256));
-                    b.regions = (b.pixels + b.regionSize - 1u) / b.regionSize;
-                    for (uint32_t g = 0; g < groups; ++g) { gb[g].regionSize = b.regionSize; gb[g].regions = b.regions; }
-                }
-                // per group: counts[4], heads[2]; word 7 of group 0 is the sticky failure flag (check_drained) and stays
-                CK(cudaMemsetAsync(b.counts, 0, 7 * sizeof(unsigned int), c->stream));
-                CK(cudaMemsetAsync(b.counts + 8, 0, 24 * sizeof(unsigned int), c->stream));
-                CK(cudaMemsetAsync(b.regionNext, 0, (size_t)b.regions * sizeof(unsigned int), c->stream));
-                const bool forked = stream_of(0) != c->stream;
-                if (forked) {
-                    CK(cudaEventRecord(c->evFork, c->stream));
-                    for (uint32_t g = 0; g < groups; ++g) CK(cudaStreamWaitEvent(c->groupStream[g], c->evFork, 0));
-                }
-                for (uint32_t g = 0; g < groups; ++g) launch_wf_shade(stream_of(g), q, gb[g], 0, true, count);
-                const uint64_t waves = waves_for(nf);
-                for (uint64_t w = 0; w < waves; ++w) {
-                    for (uint32_t g = 0; g < groups; ++g, ++pw) {
-                        cudaStream_t st = stream_of(g);
-                        gb[g].waveLog = nullptr;
-                        if (c->profile) {
-                            gb[g].waveLog = c->dWaveCounts + 2 * pw;        // the trace kernel notes its queue sizes there
-                            CK(cudaEventRecord(c->profEvents[2 * pw], st));
-                        }
-                        launch_wf_trace(st, q, gb[g], (uint32_t)(w & 1u), c->countVisits);
-                        if (c->profile) CK(cudaEventRecord(c->profEvents[2 * pw + 1], st));
-                        launch_wf_shade(st, q, gb[g], (uint32_t)w, false, count);
-                    }
-                }
-                if (forked) {
-                    for (uint32_t g = 0; g < groups; ++g) {
-                        CK(cudaEventRecord(c->evJoin[g], c->groupStream[g]));
-                        CK(cudaStreamWaitEvent(c->stream, c->evJoin[g], 0));
-                    }
-                }
-                launch_wf_resolve_samples(c->stream, q, b);
-                launched += 1 + groups * (1 + 2 * waves);
-            }
-            if (c->profile) c->profUsed = 2 * pw;
-            LAUNCHED(c, launched);
+            // queue-compacted wavefront (the production pipeline)
+            int rcw = render_wavefront(c, p, n_frames);
+            if (rcw != MRT_OK) return rcw;
         }
         CK(cudaEventRecord(c->evK1, c->stream));
         c->kernelTimed = true;
@@ -640,7 +859,10 @@ static int check_drained(mrt_ctx* c) {
     if (!c->wf.counts) return MRT_OK;
     unsigned int undrained = 0;
     CK(cudaMemcpy(&undrained, c->wf.counts + 7, sizeof undrained, cudaMemcpyDeviceToHost));
-    NEED(undrained == 0, MRT_E_STATE, "wavefront batch ended with %u rays still queued (wave bound too small)", undrained);
+    if (undrained) {            // reported once: the word is cleared so that later, complete renders are not failed for it
+        CK(cudaMemset(c->wf.counts + 7, 0, sizeof undrained));
+        return fail(MRT_E_STATE, "wavefront batch ended with %u rays still queued (wave bound too small)", undrained);
+    }
     return MRT_OK;
 }
 
@@ -776,6 +998,53 @@ int mrt_image_device_ptr(mrt_ctx* c, void** device_ptr, size_t* bytes) {
     return MRT_OK;
 }
 
+// ---- multi-GPU plumbing: everything below is enqueued on the ctx stream, so a collective issued on mrt_stream_handle()
+// between two of these calls needs no host synchronisation ------------------------------------------------------------
+int mrt_stream_handle(mrt_ctx* c, void** cuda_stream) {
+    NEED(c && cuda_stream, MRT_E_INVALID, "NULL argument");
+    *cuda_stream = (void*)c->stream;
+    return MRT_OK;
+}
+int mrt_scale_buffer(mrt_ctx* c, void* device_rgba, size_t pixels, float scale) {
+    NEED(c && device_rgba, MRT_E_INVALID, "NULL argument");
+    NEED(pixels < (1ull << 32), MRT_E_INVALID, "too many pixels");
+    CK(cudaSetDevice(c->cfg.device));
+    if (pixels) { launch_scale_image(c->stream, static_cast<float4*>(device_rgba), scale, (uint32_t)pixels); LAUNCHED(c, 1); }
+    return MRT_OK;
+}
+int mrt_shard_layout(mrt_ctx* c, uint32_t shards, uint32_t* rows_max, size_t* bytes_per_shard) {
+    NEED(c && c->dImage, MRT_E_STATE, "no size: call mrt_resize first");
+    NEED(shards >= 1, MRT_E_INVALID, "shards must be >= 1");
+    const uint32_t rm = (c->H + shards - 1) / shards;
+    if (rows_max) *rows_max = rm;
+    if (bytes_per_shard) *bytes_per_shard = (size_t)rm * c->W * sizeof(float4);
+    return MRT_OK;
+}
+int mrt_pack_rows(mrt_ctx* c, void* device_dst) {
+    NEED(c && device_dst, MRT_E_INVALID, "NULL argument");
+    NEED(c->dImage, MRT_E_STATE, "no size: call mrt_resize first");
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t rowBytes = (size_t)c->W * sizeof(float4);
+    const uint32_t rows = c->ownedRows();
+    if (rows) CK(cudaMemcpy2DAsync(device_dst, rowBytes, c->dImage + (size_t)c->rowFirst * c->W, rowBytes * c->rowStride, rowBytes, rows,
+                                   cudaMemcpyDeviceToDevice, c->stream));
+    return MRT_OK;
+}
+int mrt_unpack_rows(mrt_ctx* c, const void* device_src, uint32_t shards) {
+    NEED(c && device_src, MRT_E_INVALID, "NULL argument");
+    NEED(c->dImage, MRT_E_STATE, "no size: call mrt_resize first");
+    NEED(shards >= 1, MRT_E_INVALID, "shards must be >= 1");
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t rowBytes = (size_t)c->W * sizeof(float4);
+    const uint32_t rowsMax = (c->H + shards - 1) / shards;
+    for (uint32_t g = 0; g < shards && g < c->H; ++g) {
+        const uint32_t rows = (c->H - g + shards - 1) / shards;
+        CK(cudaMemcpy2DAsync(c->dImage + (size_t)g * c->W, rowBytes * shards, static_cast<const char*>(device_src) + (size_t)g * rowsMax * rowBytes,
+                             rowBytes, rowBytes, rows, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    return MRT_OK;
+}
+
 static int buffer_of(mrt_ctx* c, uint32_t which, void** p, size_t* bytes) {
     size_t n = (size_t)c->W * c->H;
     switch (which) {
@@ -815,6 +1084,13 @@ int mrt_get_stats(mrt_ctx* c, mrt_stats* out) {
     c->stats.primary_rays = h[0]; c->stats.shadow_rays = h[1]; c->stats.nodes_visited = h[2]; c->stats.triangles_tested = h[3];
     if (c->timed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->ev0, c->ev1)); c->stats.last_render_ms = ms; }
     if (c->kernelTimed) { float ms = 0; CK(cudaEventElapsedTime(&ms, c->evK0, c->evK1)); c->stats.last_kernel_ms = ms; }
+    {   // waves: graph replays count their launches on the device
+        unsigned int ctl[MRT_CTL_WORDS] = {};
+        if (c->wf.ctl) CK(cudaMemcpy(ctl, c->wf.ctl, sizeof ctl, cudaMemcpyDeviceToHost));
+        c->stats.waves_traced = ctl[MRT_CTL_WAVES];
+        c->graphKernels = (uint64_t)ctl[MRT_CTL_GRAPH_TRACES] * c->kernelsPerWave;
+    }
+    c->stats.tail_waves = 0;
     if (c->profUsed) {
         std::vector<unsigned int> wc(c->profUsed);
         CK(cudaMemcpy(wc.data(), c->dWaveCounts, c->profUsed * sizeof(unsigned int), cudaMemcpyDeviceToHost));
@@ -826,19 +1102,22 @@ int mrt_get_stats(mrt_ctx* c, mrt_stats* out) {
             if (wc[2 * w] + wc[2 * w + 1] == 0) continue;                 // empty wave: the kernel returned at once
             float ms = 0; CK(cudaEventElapsedTime(&ms, c->profEvents[2 * w], c->profEvents[2 * w + 1]));
             sum += ms; ++n;
+            if (2u * wc[2 * w] < c->wf.slots) c->stats.tail_waves += 1;                 // fewer extension rays than half the path slots
             if (log) fprintf(log, "%zu,%u,%u,%.4f\n", w, wc[2 * w], wc[2 * w + 1], ms);
         }
         if (log) fclose(log);
         c->stats.profile_trace_ms = (float)sum; c->stats.profile_trace_launches = n;
     }
     *out = c->stats;
+    out->kernel_launches += c->graphKernels;
     return MRT_OK;
 }
 int mrt_reset_stats(mrt_ctx* c) {
     NEED(c, MRT_E_INVALID, "ctx is NULL");
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaMemsetAsync(c->dCounters, 0, 4 * sizeof(unsigned long long), c->stream));
-    c->stats.kernel_launches = 0; c->stats.frames_rendered = 0;
+    if (c->wf.ctl) CK(cudaMemsetAsync(c->wf.ctl + MRT_CTL_GRAPH_TRACES, 0, 2 * sizeof(unsigned int), c->stream));
+    c->stats.kernel_launches = 0; c->stats.frames_rendered = 0; c->graphKernels = 0;
     return MRT_OK;
 }
 
@@ -849,13 +1128,15 @@ static int intersect_host_impl(mrt_ctx* c, const void* rays, size_t stride, uint
     if (count == 0) return MRT_OK;
     CK(cudaSetDevice(c->cfg.device));
     void* dR = nullptr; mrt_intersection* dO = nullptr;
-    CK(cudaMalloc(&dR, (size_t)count * stride));
-    CK(cudaMalloc(&dO, (size_t)count * sizeof(mrt_intersection)));
-    CK(cudaMemcpyAsync(dR, rays, (size_t)count * stride, cudaMemcpyHostToDevice, c->stream));
-    Grid2D g; g.W = count; g.H = 1; g.rowFirst = 0; g.rowStride = 1;
-    launch_intersect(c->stream, c->S, dR, (uint32_t)stride, count, dO, g, false, nullptr, profile ? c->dCounters + 2 : nullptr);
-    c->stats.kernel_launches += 1;
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = cudaMalloc(&dR, (size_t)count * stride);
+    if (e == cudaSuccess) e = cudaMalloc(&dO, (size_t)count * sizeof(mrt_intersection));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dR, rays, (size_t)count * stride, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        Grid2D g; g.W = count; g.H = 1; g.rowFirst = 0; g.rowStride = 1;
+        launch_intersect(c->stream, c->S, dR, (uint32_t)stride, count, dO, g, false, nullptr, profile ? c->dCounters + 2 : nullptr);
+        c->stats.kernel_launches += 1;
+        e = cudaGetLastError();
+    }
     if (e == cudaSuccess && out) e = cudaMemcpyAsync(out, dO, (size_t)count * sizeof(mrt_intersection), cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(dR); cudaFree(dO);

@@ -319,18 +319,25 @@ void launch_display(cudaStream_t s, const float4* image, const float4* ref, floa
                     uint32_t RH, uint32_t toneMapping, uint32_t manualSRGB, uint32_t mode, float scale) {
     k_display<<<blocks_for(W * H), 256, 0, s>>>(image, ref, out, W, H, RW, RH, toneMapping, manualSRGB, mode, scale);
 }
-// MRT_FUSED_BVH=8 puts the megakernel on the wide traversal core (the like-for-like comparison with the wavefront
-// pipeline).  Default 2: the per-lane binary-tree loop, which shares neither tree nor traversal code with the
-// production path — that independence is what the "schedules agree" tests lean on.
+// The production library carries ONE megakernel: the per-lane binary-tree loop at 2 blocks per SM, which shares neither
+// tree nor traversal code with the wavefront pipeline — that independence is what the "schedules agree" tests lean on.
+// -DMRT_EXPERIMENTS adds MRT_FUSED_BVH=8 (the megakernel on the wide traversal core, the like-for-like comparison with the
+// wavefront pipeline of DESIGN.md 3) and MRT_FUSED_MINBLOCKS.
+#ifdef MRT_EXPERIMENTS
 static int fused_bvh_width() {
     static const int w = [] { const char* e = getenv("MRT_FUSED_BVH"); return (e && atoi(e) == 8) ? 8 : 2; }();
     return w;
 }
+#endif
 void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays) {
     uint32_t tilesX = (p.g.W + 7u) >> 3, tilesY = (p.ownedRows + 3u) >> 2;
     uint32_t warps = tilesX * tilesY;
     if (warps == 0 || p.nFrames == 0) return;
     uint32_t blocks = (warps + 7u) / 8u;
+    const uint32_t magic = 0x47000000u;
+#define MRT_LAUNCH_FUSED(MB, WD) do { if (countRays) k_render_fused<true, MB, WD><<<blocks, 256, 0, s>>>(p, leafMin, magic); \
+                                      else k_render_fused<false, MB, WD><<<blocks, 256, 0, s>>>(p, leafMin, magic); } while (0)
+#ifdef MRT_EXPERIMENTS
     // blocks per SM: 3 on the wide core (80 registers with some spill beat 127 registers at 2 blocks, pass AB: +17 % / +11 %)
     static const int minb = [] { const char* e = getenv("MRT_FUSED_MINBLOCKS"); int v = e ? atoi(e) : (fused_bvh_width() == 8 ? 3 : 2); return v; }();
     // vote tuning of the wide traversal core, packed as in launch_wf_trace (wavefront.cu): 10 lanes / ratio 7
@@ -339,24 +346,24 @@ void launch_render_fused(cudaStream_t s, const RenderParams& p, bool countRays) 
         int l = a ? atoi(a) : 10, r = b ? atoi(b) : 7;
         return (uint32_t)(l < 1 ? 1 : (l > 32 ? 32 : l)) | ((uint32_t)(r < 0 ? 0 : (r > 255 ? 255 : r)) << 8);
     }();
-    const uint32_t magic = 0x47000000u;
-#define MRT_LAUNCH_FUSED(MB, WD) do { if (countRays) k_render_fused<true, MB, WD><<<blocks, 256, 0, s>>>(p, leafMin, magic); \
-                                      else k_render_fused<false, MB, WD><<<blocks, 256, 0, s>>>(p, leafMin, magic); } while (0)
     if (fused_bvh_width() == 8) {
         if (minb >= 4) MRT_LAUNCH_FUSED(4, true); else if (minb == 3) MRT_LAUNCH_FUSED(3, true); else MRT_LAUNCH_FUSED(2, true);
-    } else {
-        if (minb >= 4) MRT_LAUNCH_FUSED(4, false); else if (minb == 3) MRT_LAUNCH_FUSED(3, false); else MRT_LAUNCH_FUSED(2, false);
+        return;
     }
+    if (minb >= 4) { MRT_LAUNCH_FUSED(4, false); return; }
+    if (minb == 3) { MRT_LAUNCH_FUSED(3, false); return; }
+#else
+    const uint32_t leafMin = 10u | (7u << 8);
+#endif
+    MRT_LAUNCH_FUSED(2, false);
 #undef MRT_LAUNCH_FUSED
 }
 int fused_kernel_info(int* regs, int* maxBlocksPerSM) {
     cudaFuncAttributes a;
-    const bool wide = fused_bvh_width() == 8;
-    cudaError_t e = wide ? cudaFuncGetAttributes(&a, k_render_fused<true, 2, true>) : cudaFuncGetAttributes(&a, k_render_fused<true, 2, false>);
+    cudaError_t e = cudaFuncGetAttributes(&a, k_render_fused<true, 2, false>);
     if (e != cudaSuccess) return (int)e;
     *regs = a.numRegs;
-    return wide ? (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true, 2, true>, 256, 0)
-                : (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true, 2, false>, 256, 0);
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(maxBlocksPerSM, k_render_fused<true, 2, false>, 256, 0);
 }
 
 }  // namespace mrt

@@ -75,7 +75,35 @@ struct WfBuffers {
     uint32_t slotBase;       // first slot of the group in the whole slot array (multiple of 256)
     const unsigned int* allCounts; uint32_t groups;   // every group's counts block (8 words each), for the drain check
     unsigned int* waveLog;                            // profile mode: where THIS trace launch notes its two queue sizes (else null)
+    // batch control block (device), see MRT_CTL_*: k_wf_shade counts the samples it parks, block 0 of k_wf_trace decides
+    // whether the batch is over (nothing queued and `expected` samples parked) and then ends the graph's WHILE loop /
+    // tells the polling host loop to stop launching waves
+    unsigned int* ctl;
+    uint32_t expected;               // samples the batch must finish: owned pixels x frames
+    uint32_t waveLimit;              // trace launches after which the loop ends regardless (failure: k_wf_resolve_samples flags it)
+    unsigned long long condHandle;   // cudaGraphConditionalHandle of the WHILE node that repeats the wave pair (0 = host loop)
+    volatile unsigned int* hostStop; // mapped host word: receives batchSerial when the batch is over (host loop only; else null)
+    uint32_t batchSerial;
+    // ray ordering (MRT_WF_SORT): shade appends (slot, key) to the staging arrays and counts keys; k_wf_sort scatters the
+    // slots into the queues bucket by bucket, so that a trace warp's refills pull rays that start in the same cell of
+    // the scene box with the same direction octant
+    uint32_t sortBits;               // grid bits per axis (0 = ordering off)
+    uint32_t sortMode;               // bit 0: octant-major keys (else cell-major)
+    uint32_t* sortSlot[2];           // [0 ext, 1 shadow] unsorted slot ids of the wave being built
+    uint32_t* sortKey[2];            //                   their keys
+    unsigned int* sortHist;          // [2][buckets] key counts, then [2][buckets] scatter cursors
+    float sortLo[3], sortScale[3];   // cell = (origin - lo) * scale, clamped
 };
+#define MRT_CTL_DONE 0          /* samples parked so far in this batch */
+#define MRT_CTL_WAVES 1         /* trace launches of this batch that found rays */
+#define MRT_CTL_FINISHED 2      /* 1 once the trace kernel has seen the end of the batch */
+#define MRT_CTL_LAUNCHES 3      /* trace launches of this batch, empty ones included (the wave limit counts these) */
+#define MRT_CTL_BATCH_WORDS 4   /* words 0..3 are zeroed at the start of every batch */
+#define MRT_CTL_GRAPH_TRACES 4  /* trace launches made by graph replays since mrt_reset_stats (kernel_launches accounting) */
+#define MRT_CTL_GRAPH_WAVES 5   /* ... of which found rays */
+#define MRT_CTL_WORDS 8
+__host__ __device__ inline uint32_t wf_sort_buckets(uint32_t bits) { return bits ? 8u << (3u * bits) : 0u; }
+void launch_wf_sort(cudaStream_t s, const WfBuffers& b, uint32_t outParity);
 void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool first, bool countRays);
 void launch_wf_trace(cudaStream_t s, const RenderParams& p, const WfBuffers& b, uint32_t wave, bool countVisits);
 void launch_wf_resolve_samples(cudaStream_t s, const RenderParams& p, const WfBuffers& b);

@@ -52,7 +52,8 @@ class Stats(C.Structure):
                 ("last_render_ms", C.c_float), ("bvh_nodes", C.c_uint32), ("bvh_depth", C.c_uint32),
                 ("bvh_sah_cost", C.c_float), ("bvh_build_ms", C.c_float), ("last_kernel_ms", C.c_float),
                 ("bvh8_nodes", C.c_uint32), ("bvh8_depth", C.c_uint32), ("profile_trace_ms", C.c_float),
-                ("profile_trace_launches", C.c_uint32)]
+                ("profile_trace_launches", C.c_uint32), ("bvh8_build_ms", C.c_float), ("waves_traced", C.c_uint32),
+                ("tail_waves", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class SceneView(C.Structure):
@@ -91,6 +92,10 @@ SIGNATURES = {
     "mrt_destroy": (C.c_int, [_P]),
     "mrt_set_scene": (C.c_int, [_P, _P, _U32, _P, _U32, _P, _P, _U32, _P, _U32]),
     "mrt_set_scene_from": (C.c_int, [_P, _P]),
+    "mrt_scene_prepare": (C.c_int, [_P, _U32, _P, _U32, _P, _P, _U32, _P, _U32, _U32, _U32, C.POINTER(_P)]),
+    "mrt_scene_prepare_from": (C.c_int, [_P, _U32, C.POINTER(_P)]),
+    "mrt_set_prepared_scene": (C.c_int, [_P, _P]),
+    "mrt_prepared_scene_destroy": (None, [_P]),
     "mrt_resize": (C.c_int, [_P, _U32, _U32]),
     "mrt_set_noise": (C.c_int, [_P, _U32, _P]),
     "mrt_set_row_shard": (C.c_int, [_P, _U32, _U32]),
@@ -116,6 +121,11 @@ SIGNATURES = {
     "mrt_checkpoint_load": (C.c_int, [_P, C.c_char_p, C.POINTER(_U32)]),
     "mrt_clear_image": (C.c_int, [_P]),
     "mrt_image_device_ptr": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_SZ)]),
+    "mrt_stream_handle": (C.c_int, [_P, C.POINTER(_P)]),
+    "mrt_scale_buffer": (C.c_int, [_P, _P, _SZ, _F]),
+    "mrt_shard_layout": (C.c_int, [_P, _U32, C.POINTER(_U32), C.POINTER(_SZ)]),
+    "mrt_pack_rows": (C.c_int, [_P, _P]),
+    "mrt_unpack_rows": (C.c_int, [_P, _P, _U32]),
     "mrt_read_buffer": (C.c_int, [_P, _U32, _P, _SZ]),
     "mrt_write_buffer": (C.c_int, [_P, _U32, _P, _SZ]),
     "mrt_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),

@@ -3,18 +3,24 @@
 The reference is single-device (one MTLCommandQueue, renderer/Renderer.mm:153); every pixel-sample depends only on
 (x, y, frameIndex) and the shared noise slots, so the path shards without any exchange inside a frame:
 
-  * sample (spp) sharding — rank g of N renders frames first+g, first+g+N, ... into a SUM image
-    (MRT_ACCUM_SUM), one all-reduce(sum) of the W*H*float4 image, then scale by 1/total frames.  Differs from the
-    sequential running mean of Shaders.metal:241-247 only by fp32 rounding.
-  * row sharding — rank g owns rows y with y % N == g and runs every frame with the reference's running mean; the
-    images are combined with one all-reduce(sum) as well (rows not owned stay zero), bit-identical to one GPU.
+  * sample (spp) sharding — rank g of N renders frames first+g, first+g+N, ... into its own SUM image (MRT_ACCUM_SUM,
+    kept across steps), then ONE all-reduce(sum) of a copy of that image and a scale by 1 / (all frames so far).  The
+    result is the mean over every frame rendered since the start, whatever the number of steps; it differs from the
+    sequential running mean of Shaders.metal:241-247 only by fp32 re-association.
+  * row sharding — rank g owns rows y with y % N == g and runs every frame with the reference's running mean; the owned
+    rows are packed, all-gathered and scattered back into every rank's image ("bit-exact mode").  The
+    owned rows are never overwritten by the collective, so any number of steps stays bit-identical to one GPU.
 
-`backend` only needs torch.distributed-style all_reduce on a tensor viewing the image; on the GPU box that is NCCL over
-NVLink on the device image (no host copy), in the CPU tests it is gloo on a host copy.  The renderer is duck-typed
-(draw / clear_image / scale_image / set_row_shard / set_accumulate_mode), so the same code drives the CUDA Renderer
-and, inside tests/, the CPU checker.
+The same `ShardedRenderer.step` is what bench.py times on NCCL, what tests/test_distributed_gloo.py runs on gloo with
+the CPU checker standing in for the renderer, and what tests/test_gpu_sharded.py runs with two contexts on one GPU.
+It talks to the renderer through an *endpoint* (CudaEndpoint below; the tests have their own for the checker) and to
+the other ranks through a *collective* (TorchCollective = torch.distributed: NCCL over NVLink on the device buffers,
+gloo on host tensors).
 """
+import contextlib
 import dataclasses
+
+import numpy as np
 
 from . import _lib as L
 
@@ -48,46 +54,138 @@ def rows_owned(height, rank, world):
     return range(rank, height, world)
 
 
+class TorchCollective:
+    """torch.distributed on the default process group: NCCL for device tensors, gloo for host tensors."""
+
+    def all_reduce(self, t):
+        import torch.distributed as dist
+        dist.all_reduce(t)
+
+    def all_gather(self, out, inp):
+        import torch.distributed as dist
+        dist.all_gather_into_tensor(out, inp)
+
+
+class CudaEndpoint:
+    """The CUDA Renderer as ShardedRenderer sees it.  torch is plumbing here: it owns the reduce / gather buffers and
+    issues the collective; every copy, pack, scale and the collective itself are enqueued on the ctx's own stream
+    (mrt_stream_handle), so a step has no host synchronisation until the caller reads the result."""
+
+    def __init__(self, renderer, device):
+        import torch
+        self.r, self.device, self.torch = renderer, device, torch
+        self._stream = torch.cuda.ExternalStream(renderer.stream_handle(), device=torch.device("cuda", device))
+        ptr, nbytes = renderer.image_device_ptr()
+        h, w = renderer.height, renderer.width
+
+        class _Img:
+            __cuda_array_interface__ = {"shape": (h * w * 4,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+        self.image = torch.as_tensor(_Img(), device=f"cuda:{device}")      # aliases the accumulation image
+        self.pixels = h * w
+
+    def stream(self):
+        return self.torch.cuda.stream(self._stream)
+
+    def new_buffer(self, floats):
+        return self.torch.empty(floats, dtype=self.torch.float32, device=f"cuda:{self.device}")
+
+    def image_to(self, buf):
+        with self.stream():
+            buf.copy_(self.image, non_blocking=True)
+
+    def scale(self, buf, scale):
+        self.r.scale_buffer(buf.data_ptr(), self.pixels, scale)
+
+    def shard_layout(self, shards):
+        rows, nbytes = self.r.shard_layout(shards)
+        return rows, nbytes // 4
+
+    def pack_rows(self, buf):
+        self.r.pack_rows(buf.data_ptr())
+
+    def unpack_rows(self, buf, shards):
+        self.r.unpack_rows(buf.data_ptr(), shards)
+
+    def load_noise(self, slot, tile):
+        if isinstance(tile, np.ndarray):
+            self.r.update_noise(slot, tile)
+        else:                               # raw host or device address; stays valid until the step is synchronised
+            self.r.update_noise_from(slot, tile)
+
+    def read(self, buf, host_tensor=None):
+        """Synchronise the ctx stream and return the (H, W, 4) result as numpy (through `host_tensor` if given)."""
+        with self.stream():
+            if host_tensor is None:
+                host_tensor = self.torch.empty(buf.shape, dtype=self.torch.float32, pin_memory=True)
+            host_tensor.view(-1).copy_(buf, non_blocking=True)
+        self.r.sync()
+        return host_tensor.numpy().reshape(self.r.height, self.r.width, 4)
+
+
 class ShardedRenderer:
-    """Drives one rank's renderer and the per-step collective.
+    """Drives one rank's renderer and the per-step collective; see the module docstring for the two modes."""
 
-    all_reduce(renderer) must sum the renderer's image over all ranks in place (see bench.py for the NCCL version on
-    the device pointer, tests/test_distributed_gloo.py for the gloo version)."""
-
-    def __init__(self, renderer, rank, world, all_reduce, mode="samples"):
+    def __init__(self, endpoint, rank, world, collective=None, mode="samples"):
         if mode not in ("samples", "rows"):
             raise ValueError("mode must be 'samples' or 'rows'")
-        self.r, self.rank, self.world, self.all_reduce, self.mode = renderer, rank, world, all_reduce, mode
+        self.ep, self.rank, self.world, self.mode = endpoint, rank, world, mode
+        self.coll = collective or TorchCollective()
         self.next_frame = 0
+        self.total_frames = 0
+        self.result = None              # samples mode: the reduced, normalised image of all steps so far (device buffer)
+        self._send = self._recv = None  # rows mode: packed rows of this rank / of every rank
+        self.time_events = None         # (a, b): record the renderer's event markers a / b on the ctx stream around the collective
         if world > 1:
             if mode == "samples":
-                renderer.set_accumulate_mode(L.ACCUM_SUM)
+                endpoint.r.set_accumulate_mode(L.ACCUM_SUM)
+                self.result = endpoint.new_buffer(endpoint.r.width * endpoint.r.height * 4)
             else:
-                renderer.set_row_shard(rank, world)
+                endpoint.r.set_row_shard(rank, world)
+                _, floats = endpoint.shard_layout(world)
+                self._send = endpoint.new_buffer(floats)
+                self._recv = endpoint.new_buffer(floats * world)
 
-    def step(self, frames_per_rank, noise_tiles=None, lead_in=None):
-        """Render one step.  noise_tiles: tiles for frames next_frame+rank ... (FramePlan.span of them) in 'samples'
-        mode, tiles for next_frame ... next_frame+frames_per_rank-1 in 'rows' mode.  lead_in: {frame: tile} for
-        lead_in_frames(first frame of this rank) — needed in 'samples' mode, where a rank skips frames.
-        Returns the FramePlan used."""
+    def step(self, frames_per_rank, noise_tiles=None, lead_in=None, sync=False):
+        """Render one step and run its collective.  noise_tiles: tiles for frames next_frame+rank ... (FramePlan.span of
+        them) in 'samples' mode, tiles for next_frame ... next_frame+frames_per_rank-1 in 'rows' mode (array or raw
+        address).  lead_in: {frame: tile or address} for lead_in_frames(first frame of this rank) — needed in 'samples'
+        mode, where a rank skips frames.  Asynchronous unless sync; returns the FramePlan used."""
+        ep, r = self.ep, self.ep.r
         if self.world == 1:
             plan = FramePlan(self.next_frame, frames_per_rank, 1, frames_per_rank, frames_per_rank)
-            self.r.draw(frames_per_rank, noise_tiles, first_frame=plan.first_frame, frame_stride=1)
-            self.next_frame += frames_per_rank
-            return plan
-        if self.mode == "samples":
+            r.draw(frames_per_rank, noise_tiles, first_frame=plan.first_frame, frame_stride=1, sync=False)
+        elif self.mode == "samples":
             plan = plan_sample_shard(self.next_frame, frames_per_rank, self.rank, self.world)
             for f in lead_in_frames(plan.first_frame):
                 if lead_in is not None and f in lead_in:
-                    self.r.update_noise(f % 3, lead_in[f])
-            self.r.clear_image()
-            self.r.draw(plan.n_frames, noise_tiles, first_frame=plan.first_frame, frame_stride=plan.frame_stride)
-            self.all_reduce(self.r)
-            self.r.scale_image(1.0 / plan.total_frames)
-            self.next_frame += plan.total_frames
+                    ep.load_noise(f % 3, lead_in[f])
+            r.draw(plan.n_frames, noise_tiles, first_frame=plan.first_frame, frame_stride=plan.frame_stride, sync=False)
+            ep.image_to(self.result)                      # the rank's own sum keeps growing; the reduce works on a copy
+            if self.time_events:
+                r.event_record(self.time_events[0])
+            with ep.stream():
+                self.coll.all_reduce(self.result)
+            if self.time_events:
+                r.event_record(self.time_events[1])
+            ep.scale(self.result, 1.0 / (self.total_frames + plan.total_frames))
         else:
             plan = FramePlan(self.next_frame, frames_per_rank, 1, frames_per_rank, frames_per_rank)
-            self.r.draw(frames_per_rank, noise_tiles, first_frame=plan.first_frame, frame_stride=1)
-            self.all_reduce(self.r)             # rows this rank does not own are zero
-            self.next_frame += frames_per_rank
+            r.draw(frames_per_rank, noise_tiles, first_frame=plan.first_frame, frame_stride=1, sync=False)
+            ep.pack_rows(self._send)
+            if self.time_events:
+                r.event_record(self.time_events[0])
+            with ep.stream():
+                self.coll.all_gather(self._recv, self._send)
+            if self.time_events:
+                r.event_record(self.time_events[1])
+            ep.unpack_rows(self._recv, self.world)
+        self.next_frame += plan.total_frames
+        self.total_frames += plan.total_frames
+        if sync:
+            r.sync()
         return plan
+
+    def output(self):
+        """Device buffer holding the current image of the whole job: the reduced mean ('samples', world > 1) or the
+        renderer's own image."""
+        return self.result if (self.world > 1 and self.mode == "samples") else self.ep.image

@@ -187,6 +187,28 @@ class Renderer:
         L.check(L.lib().mrt_image_device_ptr(self._ctx, C.byref(p), C.byref(n)))
         return p.value, n.value
 
+    # ---- multi-GPU plumbing (all enqueued on the ctx stream) -------------------------------------------
+    def stream_handle(self):
+        """The ctx's cudaStream_t as an integer (for torch.cuda.ExternalStream / ncclAllReduce)."""
+        p = C.c_void_p()
+        L.check(L.lib().mrt_stream_handle(self._ctx, C.byref(p)))
+        return p.value or 0
+
+    def scale_buffer(self, device_address, pixels, scale):
+        """rgb *= scale, alpha = 1 on a device buffer of `pixels` float4 (the reduced sum image)."""
+        L.check(L.lib().mrt_scale_buffer(self._ctx, C.c_void_p(int(device_address)), pixels, scale))
+
+    def shard_layout(self, shards):
+        rows, nbytes = C.c_uint32(), C.c_size_t()
+        L.check(L.lib().mrt_shard_layout(self._ctx, shards, C.byref(rows), C.byref(nbytes)))
+        return rows.value, nbytes.value
+
+    def pack_rows(self, device_address):
+        L.check(L.lib().mrt_pack_rows(self._ctx, C.c_void_p(int(device_address))))
+
+    def unpack_rows(self, device_address, shards):
+        L.check(L.lib().mrt_unpack_rows(self._ctx, C.c_void_p(int(device_address)), shards))
+
     def read_buffer(self, which):
         n = self.width * self.height
         if which == L.BUF_IMAGE:

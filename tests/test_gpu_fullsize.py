@@ -97,14 +97,22 @@ print("variant ok", sa["kernel_launches"])
     {"MRT_TRACE_TQ": "32"}, {"MRT_TRACE_TQ": "1"}, {"MRT_TRACE_TQ": "96", "MRT_TRACE_COUNT": "1"},   # warp-wide triangle queue
     {"MRT_BVH_BINS": "64"}, {"MRT_BVH_BINS": "8,32"},                   # SAH bins of the binary builder: fixed / other candidates for the sampled selection
     {"MRT_FUSED_BVH": "8"}, {"MRT_FUSED_BVH": "8", "MRT_FUSED_MINBLOCKS": "2"},   # megakernel on the wide traversal core (default: binary tree)
+    {"MRT_WF_GRAPH": "0"}, {"MRT_WF_GRAPH": "0", "MRT_WF_SORT": "2"},   # polling host loop instead of the WHILE graph
+    {"MRT_WF_SORT": "0"}, {"MRT_WF_SORT": "1"}, {"MRT_WF_SORT": "2", "MRT_WF_SORT_MODE": "1"}, {"MRT_WF_SORT": "3"},   # ray ordering grid
+    {"MRT_WF_SORT": "2", "MRT_WF_SPLIT": "2"}, {"MRT_WF_SORT": "3", "MRT_TRACE_TQ": "32"},
 ], ids=lambda e: ",".join(f"{k[4:].lower()}={v}" for k, v in e.items()))
 def test_tuning_switches_do_not_change_the_bits(env):
-    """Every scheduling knob of csrc/wavefront.cu / api.cu (read once per process from the environment) must leave the
-    image and the ray counts bit-identical: the wavefront render under the knob == the megakernel render."""
+    """Every scheduling knob of csrc/wavefront.cu / api.cu / bvh.cpp (read once per process from the environment) must
+    leave the image and the ray counts bit-identical: the wavefront render under the knob == the megakernel render.
+    Runs against the EXPERIMENTS build (lib/libmrt_b200_exp.so, `make exp`): the production library compiles the
+    rejected kernel variants and most of their knobs out."""
     import os, pathlib, subprocess, sys
     root = pathlib.Path(__file__).resolve().parent.parent
+    exp = root / "metal-renderer_b200" / "lib" / "libmrt_b200_exp.so"
+    if not exp.exists():
+        subprocess.check_call(["make", "-s", "-C", str(root / "metal-renderer_b200"), "lib/libmrt_b200_exp.so"])
     script = _VARIANT_SCRIPT % dict(pkg=str(root / "metal-renderer_b200"), tests=str(root / "tests"))
-    out = subprocess.run([sys.executable, "-c", script], env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
+    out = subprocess.run([sys.executable, "-c", script], env=dict(os.environ, MRT_B200_LIB=str(exp), **env), capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "variant ok" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
 
 

@@ -86,7 +86,11 @@ def test_config1_cornell_256_16spp_depth4_bit_exact(pipeline):
     assert_bits(gi, oi, "image")
     st, oc = r.stats(), o.counts()
     assert (st["primary_rays"], st["shadow_rays"]) == (oc["primary_rays"], oc["shadow_rays"])
-    assert st["kernel_launches"] == (1 if pipeline == m.PIPELINE_MEGAKERNEL else 2 + 2 * (16 * 4 + 4 + 2))
+    if pipeline == m.PIPELINE_MEGAKERNEL:
+        assert st["kernel_launches"] == 1
+    else:       # first shade + resolve + (trace, shade) per wave; the WHILE graph stops within two launches of the last
+        # wave that had rays, far below the static bound of 16 * 4 + 4 + 2 waves
+        assert 2 + 2 * st["waves_traced"] <= st["kernel_launches"] <= 2 + 2 * (st["waves_traced"] + 3) and 16 <= st["waves_traced"] <= 70
     # primary-hit triangle IDs: bit-equal on 100% of pixels
     r2, o2 = setup_pair(scene, 256, 256)
     r2.raygen(0); o2.raygen(0); r2.intersect(); o2.intersect()
