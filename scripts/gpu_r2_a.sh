@@ -40,3 +40,5 @@ for v in 0 3; do
 done
 ls -la gpurun_out | tail -20
 ( timeout 1200 python -m pytest tests/test_gpu_fullsize.py tests/test_display.py tests/test_mitsuba_sanity.py -x -q -m gpu 2>&1 | tail -15 ) | tee gpurun_out/a_pytest3.log
+( timeout 600 python bench.py --steps 1 --warmup 3 --frames 16 --no-cpu-baseline 2> gpurun_out/a_bench_smoke.err | tail -c 6000 ) | tee gpurun_out/a_bench_smoke.json
+tail -5 gpurun_out/a_bench_smoke.err
