@@ -34,6 +34,8 @@ import numpy as np  # noqa: E402
 WORKLOADS = {   # BASELINE.json configs; SURVEY.md §8(d) "Concrete inputs"
     "spheres-1m-1080p": dict(scene="spheres-1m", seed=3, width=1920, height=1080, frames=128, depth=8, config=3),
     "cornell-water-1080p": dict(scene="cornell-water", seed=2, width=1920, height=1080, frames=64, depth=8, config=2),
+    # the reference's own Media/CornellBox-Water-plastic.obj (ABI arrays committed by tests/golden/make_media_fixture.py)
+    "media-water-plastic-1080p": dict(scene="media:CornellBox-Water-plastic", seed=2, width=1920, height=1080, frames=64, depth=8, config=2),
     "cornell-256": dict(scene="cornell", seed=1, width=256, height=256, frames=16, depth=4, config=1),
     "spheres-10m-4k": dict(scene="spheres-10m", seed=4, width=3840, height=2160, frames=256, depth=8, config=4),
     "many-lights-1080p": dict(scene="many-lights", seed=5, width=1920, height=1080, frames=512, depth=8, config=5),
@@ -127,6 +129,12 @@ class ClockSampler:
         return out
 
 
+def load_scene(m, wl):
+    if wl["scene"].startswith("media:"):
+        return m.Scene.from_npz(ROOT / "tests" / "golden" / "media_water.npz", wl["scene"][6:])
+    return m.Scene.procedural(wl["scene"], wl["seed"])
+
+
 def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
@@ -140,7 +148,7 @@ def run_reference(args, wl):
     sys.path.insert(0, str(ROOT / "oracle"))
     import mrt_b200 as m
     import oracle as orc
-    scene = m.Scene.procedural(wl["scene"], wl["seed"])
+    scene = load_scene(m, wl)
     o = orc.Oracle(max_path_length=wl["depth"], threads=0)
     o.init_raytracing(scene)
     o.drawable_size_will_change(wl["width"], wl["height"])
@@ -284,7 +292,7 @@ def run_ours(args, wl):
     torch.cuda.set_device(dev)
     W, H, F, Dp = wl["width"], wl["height"], wl["frames"], wl["depth"]
     t_setup = time.perf_counter()
-    scene = m.Scene.procedural(wl["scene"], wl["seed"])
+    scene = load_scene(m, wl)
     t_scene = time.perf_counter()
     r = m.Renderer(device=dev, max_path_length=Dp)
     r.init_raytracing(scene)

@@ -32,9 +32,9 @@ __global__ void __launch_bounds__(256) k_raygen(mrt_ray* __restrict__ rays, cons
 }
 
 // ---- MPS nearest-hit stand-in over a strided ray buffer (Renderer.mm:519-523, 545-553) -------------------
-template <bool VEC, bool COUNT>
+template <bool COUNT>
 __global__ void __launch_bounds__(256) k_intersect(DeviceScene S, const char* __restrict__ rays, uint32_t stride, uint32_t count,
-                                                   mrt_intersection* __restrict__ out, Grid2D g, bool useGrid,
+                                                   mrt_intersection* __restrict__ out, Grid2D g, bool useGrid, bool vec,
                                                    unsigned long long* liveCounter, unsigned long long* visitCounters) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long nodesV = 0, trisT = 0;
@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(256) k_intersect(DeviceScene S, const char* __
     if (i < count && (!useGrid || owns_row(g, i / g.W))) {
         const char* p = rays + (size_t)i * stride;
         float4 a, b;
-        if (VEC) { a = *reinterpret_cast<const float4*>(p); b = *reinterpret_cast<const float4*>(p + 16); }
+        if (vec) { a = *reinterpret_cast<const float4*>(p); b = *reinterpret_cast<const float4*>(p + 16); }
         else {
             const float* f = reinterpret_cast<const float*>(p);
             a = make_float4(f[0], f[1], f[2], f[3]); b = make_float4(f[4], f[5], f[6], f[7]);
@@ -292,13 +292,8 @@ void launch_intersect(cudaStream_t s, const DeviceScene& S, const void* rays, ui
     if (count == 0) return;
     bool vec = (strideBytes % 16u == 0) && ((uintptr_t)rays % 16u == 0);
     const char* r = static_cast<const char*>(rays);
-    if (visitCounters) {
-        if (vec) k_intersect<true, true><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, liveCounter, visitCounters);
-        else k_intersect<false, true><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, liveCounter, visitCounters);
-    } else {
-        if (vec) k_intersect<true, false><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, liveCounter, nullptr);
-        else k_intersect<false, false><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, liveCounter, nullptr);
-    }
+    if (visitCounters) k_intersect<true><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, visitCounters);
+    else k_intersect<false><<<blocks_for(count), 256, 0, s>>>(S, r, strideBytes, count, out, g, useGrid, vec, liveCounter, nullptr);
 }
 void launch_shade(cudaStream_t s, const DeviceScene& S, const mrt_intersection* isects, mrt_ray* rays,
                   mrt_light_sampling_ray* lightRays, const float4* noiseTile, uint32_t frameIndex, uint32_t maxPathLength,

@@ -363,6 +363,7 @@ __global__ void __launch_bounds__(256, MINB) k_wf_shade(RenderParams P, WfBuffer
     }
 }
 
+#ifdef MRT_EXPERIMENTS
 // Counting sort of one wave's two queues by ray key (MRT_WF_SORT).  Every block scans the key counts itself (they are
 // complete: k_wf_shade ran before us), then places its share of the staged slots: offset of the bucket + a position
 // from the bucket's cursor, taken once per warp and key (__match_any_sync), so that a warp's rays of one key stay
@@ -406,6 +407,7 @@ __global__ void __launch_bounds__(256) k_wf_sort(WfBuffers b, uint32_t outParity
         }
     }
 }
+#endif
 
 // accumulateImage (Shaders.metal:233-249) over the batch, in frame order, one thread per owned pixel
 __global__ void __launch_bounds__(256) k_wf_resolve_samples(RenderParams P, WfBuffers b) {
@@ -539,11 +541,13 @@ void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     const uint32_t f = first ? 1u : 0u;
     // 4 blocks per SM = 64 registers with a 56-byte spill frame; 3 = 80 registers.  The kernel is latency-bound (ncu pass O:
     // 36 % warps active, long scoreboard), so occupancy wins: +3.6 % per step in pass P
-#define MRT_LAUNCH_SHADE(MB) do { \
-        if (b.sortBits) { if (countRays) k_wf_shade<true, MB, true><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave); \
-                          else           k_wf_shade<false, MB, true><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave); } \
-        else            { if (countRays) k_wf_shade<true, MB, false><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave); \
-                          else           k_wf_shade<false, MB, false><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave); } } while (0)
+#define MRT_LAUNCH_SHADE_S(MB, SORT) do { if (countRays) k_wf_shade<true, MB, SORT><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave); \
+                                          else           k_wf_shade<false, MB, SORT><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave); } while (0)
+#ifdef MRT_EXPERIMENTS
+#define MRT_LAUNCH_SHADE(MB) do { if (b.sortBits) MRT_LAUNCH_SHADE_S(MB, true); else MRT_LAUNCH_SHADE_S(MB, false); } while (0)
+#else
+#define MRT_LAUNCH_SHADE(MB) MRT_LAUNCH_SHADE_S(MB, false)      /* ray ordering (MRT_WF_SORT) lost: experiments build only */
+#endif
 #ifdef MRT_EXPERIMENTS
     static const int minb = env_int("MRT_SHADE_MINBLOCKS", 4);
     if (minb >= 5) { MRT_LAUNCH_SHADE(5); return; }
@@ -551,12 +555,17 @@ void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
 #endif
     MRT_LAUNCH_SHADE(4);
 #undef MRT_LAUNCH_SHADE
+#undef MRT_LAUNCH_SHADE_S
 }
 
 void launch_wf_sort(cudaStream_t s, const WfBuffers& b, uint32_t outParity) {
+#ifdef MRT_EXPERIMENTS
     if (!b.sortBits || b.slots == 0) return;
     const uint32_t need = (b.slots + 255u) / 256u, cap = (uint32_t)device_sms() * 4u;
     k_wf_sort<<<need < cap ? need : cap, 256, 2u * wf_sort_buckets(b.sortBits) * sizeof(uint32_t), s>>>(b, outParity);
+#else
+    (void)s; (void)b; (void)outParity;
+#endif
 }
 
 bool trace_uses_wide_bvh() { return trace_tuning().wide != 0; }

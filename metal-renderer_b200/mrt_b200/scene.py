@@ -54,6 +54,15 @@ class Scene:
         return cls._from_handle(handle, name)
 
     @classmethod
+    def from_npz(cls, path, prefix):
+        """Scene stored as ABI arrays under `prefix/` in an .npz (tests/golden/*.npz: the reference's Media files run
+        through load_obj where the reference tree is present, so that the GPU box can render them without it)."""
+        with np.load(path) as z:
+            lights = z[f"{prefix}/lights"]
+            return cls(z[f"{prefix}/vertices"], z[f"{prefix}/indices"], z[f"{prefix}/references"], z[f"{prefix}/materials"],
+                       lights, len(lights) - 1, f"{prefix} ({path})")
+
+    @classmethod
     def load_obj(cls, path):
         handle = C.c_void_p()
         L.check(L.lib().mrt_scene_load_obj(str(path).encode(), C.byref(handle)))

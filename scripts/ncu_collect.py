@@ -2,7 +2,7 @@
 """Turn one `ncu --set full` report of a steady-state k_wf_trace / k_wf_shade launch into the committed summary that
 bench.py parses for its roofline object: profiles/ncu_<kernel>_<workload>.txt.
 
-usage: ncu_collect.py <report.ncu-rep> <trace|shade> <workload> <rays_in_launch|0> "<command that was profiled>"
+usage: ncu_collect.py <report.ncu-rep> <trace|shade> <workload> <rays_in_launch|0> "<command that was profiled>" [output name]
 
 Lines `name value unit` carry the raw counters (bench.py: ncu_summary); `#` lines carry provenance — the commit the
 kernels were built from and the rays the profiled launch traced (from the wave log of the same command, so approximate:
@@ -33,9 +33,17 @@ out = [f"# ncu --set full --clock-control none --import-source on, one steady-st
        f"# command: {cmd}",
        f"# kernels built from commit {commit}{' + uncommitted changes in csrc/' if dirty else ''}",
        f"# rays_in_launch {rays:.0f}   (wave log of the same command without ncu; dynamic work claiming makes this approximate)"]
-out += ["%-90s %s %s" % (w, v[h.index(w)].replace(",", ""), u[h.index(w)]) for w in keep if w in h]
+SCALE = {"Kbyte": (1e3, "byte"), "Mbyte": (1e6, "byte"), "Gbyte": (1e9, "byte"), "Tbyte": (1e12, "byte"),
+         "us": (1e3, "ns"), "ms": (1e6, "ns"), "s": (1e9, "ns"), "usecond": (1e3, "ns"), "msecond": (1e6, "ns"), "second": (1e9, "ns"), "nsecond": (1, "ns")}
+for w in keep:                      # values normalised to bytes and nanoseconds (ncu picks a unit per value)
+    if w not in h:
+        continue
+    val, unit = v[h.index(w)].replace(",", ""), u[h.index(w)]
+    if unit in SCALE:
+        val, unit = "%.6g" % (float(val) * SCALE[unit][0]), SCALE[unit][1]
+    out.append("%-90s %s %s" % (w, val, unit))
 lines = subprocess.run([sys.executable, str(root / "scripts/ncu_lines.py"), rep, "24"], capture_output=True, text=True).stdout
-dst = root / "profiles" / f"ncu_{kernel}_{workload}.txt"
+dst = root / "profiles" / (sys.argv[6] if len(sys.argv) > 6 else f"ncu_{kernel}_{workload}.txt")
 dst.write_text("\n".join(out) + "\n\n# per-source-line summary (scripts/ncu_lines.py): share of warp instructions, lanes, share of stall samples\n"
                + "\n".join("# " + l for l in lines.splitlines()) + "\n")
 print("\n".join(out))

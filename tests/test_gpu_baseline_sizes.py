@@ -3,6 +3,8 @@ on all host cores at the config's resolution and path length — accumulated ima
 primary-hit triangle index of 100 % of the pixels (raygen + intersect on both sides).  Frames are kept to what the
 oracle renders in about a minute (it does 1080p over 1 M triangles in ~1.4 s per frame on 16 cores); the bench line
 repeats the same gate on the benchmarked workload (bench.py: `parity`)."""
+import pathlib
+
 import numpy as np
 import pytest
 
@@ -12,6 +14,7 @@ from helpers import bits_equal, setup_pair
 pytestmark = pytest.mark.gpu
 
 CONFIGS = [   # BASELINE.json configs[1..4]; SURVEY.md 8(d) "Concrete inputs"
+    pytest.param("media:CornellBox-Water-plastic", 2, 1920, 1080, 8, 2, id="config2-media-water-plastic-1080p"),   # the reference's own file
     pytest.param("cornell-water", 2, 1920, 1080, 8, 2, id="config2-cornell-water-1080p"),
     pytest.param("spheres-1m", 3, 1920, 1080, 8, 2, id="config3-spheres-1m-1080p"),
     pytest.param("spheres-10m", 4, 3840, 2160, 8, 1, id="config4-spheres-10m-4k"),
@@ -21,7 +24,10 @@ CONFIGS = [   # BASELINE.json configs[1..4]; SURVEY.md 8(d) "Concrete inputs"
 
 @pytest.mark.parametrize("name,seed,w,h,depth,frames", CONFIGS)
 def test_baseline_config_bit_exact_at_its_own_size(name, seed, w, h, depth, frames):
-    scene = m.Scene.procedural(name, seed)
+    if name.startswith("media:"):       # renderer/Media/<name>.obj through the OBJ/MTL loader, committed as ABI arrays
+        scene = m.Scene.from_npz(pathlib.Path(__file__).resolve().parent / "golden" / "media_water.npz", name[6:])
+    else:
+        scene = m.Scene.procedural(name, seed)
     r, o = setup_pair(scene, w, h, seed=seed, max_path_length=depth, renderer_kwargs=dict(pipeline=m.PIPELINE_WAVEFRONT))
     # primary hits of frame 0 through the staged entry points (the drop-in seam): 100 % of the pixels
     r.raygen(0); o.raygen(0)
