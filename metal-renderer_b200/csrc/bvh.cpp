@@ -264,7 +264,7 @@ constexpr float kCostNode = 1.0f;
 // single triangles gives 4.3 triangle + 13.0 node tests per ray instead of 6.3 + 12.1 and +4.5 % rays/s (0.3 was the
 // instruction-count ratio).
 static const float kCostPrim = getenv("MRT_BVH8_CPRIM") ? (float)atof(getenv("MRT_BVH8_CPRIM")) : 1.0f;
-// largest leaf the collapse may form (meta byte: 3-bit unary count); MRT_BVH8_MAXLEAF=1 forces single-triangle leaves
+// largest leaf the collapse may form (Bvh8Node::leafTris: three bits per slot); MRT_BVH8_MAXLEAF=1 forces single-triangle leaves
 static const uint32_t kMaxLeaf8 = getenv("MRT_BVH8_MAXLEAF") ? (uint32_t)std::min(3, std::max(1, atoi(getenv("MRT_BVH8_MAXLEAF")))) : 3u;
 
 struct Collapse {
@@ -443,15 +443,14 @@ static void build_bvh8_bins(const mrt_vertex* vertices, const uint32_t* indices,
         uint32_t triOffset = 0;
         for (int s = 0; s < 8; ++s) {
             int c = kidAt[s];
-            if (c < 0) { nd.meta[s] = 0; continue; }
+            if (c < 0) continue;
             const BuildNode& ch = b.sparse[kids[c]];
             if (col.is_leaf_child(kids[c])) {
-                nd.meta[s] = uint8_t((((1u << ch.count) - 1u) << 5) | triOffset);     // unary count, offset
+                nd.leafTris |= ((1u << ch.count) - 1u) << (3 * s);                     // unary count at the slot's three bits
                 emit_tris(ch);
                 triOffset += ch.count;
             } else {
                 nd.imask |= uint8_t(1u << s);
-                nd.meta[s] = uint8_t(0x20u | (24u + uint32_t(s)));
                 uint32_t idx = uint32_t(out.nodes.size());
                 out.nodes.push_back(Bvh8Node{});
                 queue.push_back(Item{kids[c], idx, it.depth + 1, false});
@@ -512,7 +511,7 @@ static HostHit host_trace8(const Bvh8Result& bvh, const float* o, const float* d
             uint32_t hs = bvh8_hit_slots(w, r, tmin, best.t);
             uint32_t imask = w[3] >> 24;
             gx = w[4]; gy = ((hs & imask) << 24) | imask;
-            tx = w[5]; ty = bvh8_triangle_mask(w[6], w[7], hs & ~imask);
+            tx = w[5]; ty = bvh8_triangle_mask(w[6], hs & ~imask);
         }
         while (ty) {
             int k = __builtin_ctz(ty); ty &= ty - 1;

@@ -30,7 +30,10 @@ struct Bvh8Node {
     uint8_t imask;          // bit s set: child slot s is an inner node
     uint32_t childBase;     // node index of the first inner child
     uint32_t triBase;       // triangle record index of the first triangle of this node's leaf children
-    uint8_t meta[8];        // inner: 0x20 | (24 + slot); leaf: (unary triangle count << 5) | offset from triBase; empty: 0
+    uint32_t leafTris;      // bit 3s+j: the leaf child in slot s holds more than j triangles (<= 3 per leaf).  The triangles of
+                            // a node's leaf children lie contiguously from triBase in slot order, so triangle (s, j) is
+                            // record triBase + popcount(leafTris & ((1 << (3s+j)) - 1)): no per-slot offsets, no loop
+    uint32_t reserved;
     uint8_t qlo[3][8];      // lower planes x,y,z per child slot
     uint8_t qhi[3][8];      // upper planes
 };
@@ -206,20 +209,43 @@ MRT_HD uint32_t bvh8_hit_slots(const uint32_t* w, const Ray8& r, float tmin, flo
 #endif
 }
 
-// Triangle mask (bit = offset from triBase) of the leaf children in `leafSlots`; meta bytes = w[6], w[7].
-MRT_HD uint32_t bvh8_triangle_mask(uint32_t meta0, uint32_t meta1, uint32_t leafSlots) {
-    uint32_t m = 0;
-    while (leafSlots) {
+// x (8 bits) with every bit tripled: bit s -> bits 3s, 3s+1, 3s+2 (slot mask -> positions in Bvh8Node::leafTris).  The
+// trace kernel reads this from a 1 KB shared-memory table instead (device_trace8.cuh).
+MRT_HD uint32_t mrt_spread3(uint32_t x) {
+    x = (x | (x << 8)) & 0x00F00Fu;
+    x = (x | (x << 4)) & 0x0C30C3u;
+    x = (x | (x << 2)) & 0x249249u;
+    return x * 7u;
+}
+MRT_HD uint32_t mrt_popc(uint32_t x) {
 #if defined(__CUDA_ARCH__)
-        const uint32_t s = uint32_t(__ffs(leafSlots)) - 1u;
+    return (uint32_t)__popc(x);
 #else
-        const uint32_t s = uint32_t(__builtin_ctz(leafSlots));
+    return (uint32_t)__builtin_popcount(x);
 #endif
-        leafSlots &= leafSlots - 1u;
-        const uint32_t b = mrt_byte8(meta0, meta1, s);
-        m |= (b >> 5) << (b & 0x1fu);
+}
+// Triangles (bits of Bvh8Node::leafTris) of the leaf children in `leafSlots`; triangle of bit k = record
+// triBase + bvh8_triangle_record(leafTris, k).
+MRT_HD uint32_t bvh8_leaf_triangles(uint32_t leafTris, uint32_t leafSlots) { return mrt_spread3(leafSlots) & leafTris; }
+MRT_HD uint32_t bvh8_triangle_record(uint32_t leafTris, uint32_t k) { return mrt_popc(leafTris & ((1u << k) - 1u)); }
+// The same as a mask over RECORDS (bit = offset from triBase) — the traversal variants of the experiments build and the
+// host self-test walk this one.
+MRT_HD uint32_t bvh8_triangle_mask(uint32_t leafTris, uint32_t leafSlots) {
+    uint32_t t = bvh8_leaf_triangles(leafTris, leafSlots), m = 0;
+    while (t) {
+#if defined(__CUDA_ARCH__)
+        const uint32_t k = uint32_t(__ffs(t)) - 1u;
+#else
+        const uint32_t k = uint32_t(__builtin_ctz(t));
+#endif
+        t &= t - 1u;
+        m |= 1u << bvh8_triangle_record(leafTris, k);
     }
     return m;
+}
+// (unary triangle count << 5) | offset from triBase of the leaf child in slot s (the experiments' triangle queue)
+MRT_HD uint32_t bvh8_leaf_meta(uint32_t leafTris, uint32_t s) {
+    return (((leafTris >> (3u * s)) & 7u) << 5) | bvh8_triangle_record(leafTris, 3u * s);
 }
 
 }  // namespace mrt

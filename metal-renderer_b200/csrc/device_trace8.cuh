@@ -19,9 +19,13 @@ namespace mrt {
 
 // Visiting order of child slots per ray octant: lut[c][x] = x with bit i moved to bit i ^ c.  2 KB of shared memory,
 // filled once per block by the kernel (every thread of the block must call this) and handed to the traversal.
-#define MRT_ORDER_LUT_BYTES (8 * 256)
+// Behind it, 256 words: slot mask -> the same bits tripled (mrt_spread3), which ANDed with Bvh8Node::leafTris gives the
+// triangles of the hit leaf children without a loop over the slots.  Declare the table 4-byte aligned.
+#define MRT_ORDER_LUT_BYTES (8 * 256 + 256 * 4)
 __device__ __forceinline__ void bvh8_fill_order_lut(uint8_t* lut) {
     for (uint32_t i = threadIdx.x; i < 8u * 256u; i += blockDim.x) lut[i] = (uint8_t)mrt_perm8(i & 0xffu, i >> 8);
+    uint32_t* spread = reinterpret_cast<uint32_t*>(lut + 8 * 256);
+    for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x) spread[i] = mrt_spread3(i);
     __syncthreads();
 }
 
@@ -49,7 +53,8 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
     float tmin = 0.f, tmax = 0.f;
     Ray8 r; r.ox = r.oy = r.oz = 0.f; r.invx = r.invy = r.invz = 0.f; r.negx = r.negy = r.negz = 0u; r.octInv = 0u; r.magic = magic;
     HitRec best; best.t = 0.f; best.tri = MRT_NO_HIT; best.u = best.v = 0.f;
-    uint32_t gx = 0, gy = 0, tx = 0, ty = 0;
+    uint32_t gx = 0, gy = 0, tx = 0, ty = 0, tv = 0;       // tv: leafTris of the node T came from (bit -> record offset)
+    const uint32_t* spreadLut = reinterpret_cast<const uint32_t*>(orderLut + 8 * 256);
     uint2 stack[MRT_STACK8];
     int sp = 0;
 
@@ -91,8 +96,9 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
             const bool wantNode = alive && ty == 0;        // invariant: an alive lane with T empty has inner hits in G
             const unsigned mN = __ballot_sync(0xffffffffu, wantNode);
             const unsigned mT = __ballot_sync(0xffffffffu, wantTri);
-            if ((mN | mT) == 0) break;
+            // mN | mT = the lanes still alive: back to the refill when the warp runs thin (or has nothing left)
             const int nT = __popc(mT), nN = __popc(mN);
+            if (nN + nT == 0 || (!exhausted && nN + nT < (int)refillBelow)) break;
             if (mN != 0 && nT < (int)leafMin && (triRatio == 0 || 16 * nT < triRatio * nN)) {
                 if (wantNode) {
                     // nearest unvisited inner child in octant order (G keeps its hits in slot space)
@@ -115,7 +121,7 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
                     const uint32_t hs = bvh8_hit_slots(w, r, tmin, best.t);
                     const uint32_t imask = w[3] >> 24;
                     gx = w[4]; gy = ((hs & imask) << 24) | imask;
-                    tx = w[5]; ty = bvh8_triangle_mask(w[6], w[7], hs & ~imask);
+                    tx = w[5]; tv = w[6]; ty = spreadLut[hs & ~imask] & tv;
                     if (ty == 0 && !(gy & 0xff000000u)) {                       // nothing hit below: next group or done
                         if (sp > 0) { uint2 e = stack[--sp]; gx = e.x; gy = e.y; }
                         else { if (best.tri == MRT_NO_HIT) best.t = -1.0f; io.store(tag, target, best); alive = false; }
@@ -127,7 +133,7 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
                 const int k = __ffs(ty) - 1;
                 ty &= ty - 1u;
                 if (COUNT) ++nTris;
-                triangle_test(tris, tx + uint32_t(k), o, d, tmin, tmax, best);
+                triangle_test(tris, tx + bvh8_triangle_record(tv, uint32_t(k)), o, d, tmin, tmax, best);
                 if (target != MRT_NO_HIT && best.tri != target) {                // any-hit job: occluded, done
                     ty = 0; io.store(tag, target, best); alive = false;
                 } else if (ty == 0 && !(gy & 0xff000000u)) {
@@ -135,8 +141,6 @@ __device__ __forceinline__ void trace_persistent8(const float4* __restrict__ nod
                     else { if (best.tri == MRT_NO_HIT) best.t = -1.0f; io.store(tag, target, best); alive = false; }
                 }
             }
-            const unsigned a2 = __ballot_sync(0xffffffffu, alive);
-            if (a2 == 0 || (!exhausted && __popc(a2) < (int)refillBelow)) break;
         }
     }
     if (COUNT && visits) {

@@ -171,14 +171,14 @@ __device__ __forceinline__ void trace_persistent8q(const float4* __restrict__ no
                     const uint32_t imask = w[3] >> 24;
                     gx = w[4]; gy = ((hs & imask) << 24) | imask;
                     tx = w[5]; ty = hs & ~imask;                               // ty: hit LEAF SLOTS of this node (not yet triangles)
-                    m0 = w[6]; m1 = w[7];
+                    m0 = w[6]; m1 = 0u;                                        // m0: leafTris of the node
                     if (!(gy & 0xff000000u) && sp > 0) { uint2 e = stack[--sp]; gx = e.x; gy = e.y; }   // G always holds the next inner work
                 }
                 // ---- queue the triangles just found: count them without a loop (a leaf's meta byte carries its triangle
                 // count in unary in bits 5-7), reserve queue positions with one shared-memory atomic per lane, then one
                 // pass over the hit leaf slots writes the pairs ----
                 {
-                    const uint32_t c = ty ? __popc(m0 & tq_expand4(ty) & 0xe0e0e0e0u) + __popc(m1 & tq_expand4(ty >> 4) & 0xe0e0e0e0u) : 0u;
+                    const uint32_t c = (uint32_t)__popc(bvh8_leaf_triangles(m0, ty));
                     const uint32_t totalNew = __reduce_add_sync(0xffffffffu, c);
                     if (qTail - qHead + totalNew <= MRT_TQ_CAP) {
                         if (c != 0u) {
@@ -188,7 +188,7 @@ __device__ __forceinline__ void trace_persistent8q(const float4* __restrict__ no
                             do {
                                 const uint32_t sl = uint32_t(__ffs(ty)) - 1u;
                                 ty &= ty - 1u;
-                                const uint32_t mb = mrt_byte8(m0, m1, sl);
+                                const uint32_t mb = bvh8_leaf_meta(m0, sl);
                                 const uint32_t e = laneTag | (tx + (mb & 0x1fu));
                                 W->q[pos & (MRT_TQ_CAP - 1u)] = e;
                                 if (mb & 0x40u) W->q[(pos + 1u) & (MRT_TQ_CAP - 1u)] = e + 1u;
@@ -198,7 +198,7 @@ __device__ __forceinline__ void trace_persistent8q(const float4* __restrict__ no
                         }
                         qTail += totalNew;
                     } else {
-                        ty = bvh8_triangle_mask(m0, m1, ty);
+                        ty = bvh8_triangle_mask(m0, ty);
                         for (;;) {                          // one pair per lane per round, draining the queue when it is full
                             const unsigned mP = __ballot_sync(0xffffffffu, ty != 0u);
                             if (mP == 0) break;
@@ -341,7 +341,7 @@ __device__ __forceinline__ void trace_persistent8d(const float4* __restrict__ no
                     const uint32_t imask = w[3] >> 24;
                     gx = w[4]; gy = ((hs & imask) << 24) | imask;
                     if (!(gy & 0xff000000u) && sp > 0) { uint2 e = stack[--sp]; gx = e.x; gy = e.y; }   // G always holds the next inner work
-                    const uint32_t nt = bvh8_triangle_mask(w[6], w[7], hs & ~imask);
+                    const uint32_t nt = bvh8_triangle_mask(w[6], hs & ~imask);
                     if (nt != 0u) {
                         if (ty == 0u) { tx = w[5]; ty = nt; }
                         else { tq[(th + tn) % MRT_TQUEUE] = make_uint2(w[5], nt); ++tn; }

@@ -191,7 +191,7 @@ struct FusedIO {
 
 template <bool COUNT, int MINB, bool WIDE>
 __global__ void __launch_bounds__(256, MINB) k_render_fused(RenderParams P, uint32_t leafMin, uint32_t magic) {
-    __shared__ uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 1];
+    __shared__ __align__(16) uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 4];
     __shared__ unsigned int warpHead[8];
     if (WIDE) bvh8_fill_order_lut(orderLut);
     const uint32_t lane = threadIdx.x & 31u;

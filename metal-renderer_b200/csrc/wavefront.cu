@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(128, MINB) k_intersect_persistent(DeviceScene 
                                                                     bool useGrid, bool vec, unsigned long long* liveCounter,
                                                                     unsigned int* head, uint32_t refillBelow, uint32_t leafMin, uint32_t magic) {
     StridedIO io; io.rays = rays; io.stride = stride; io.out = out; io.g = g; io.useGrid = useGrid; io.vec = vec; io.live = 0;
-    __shared__ uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 1];
+    __shared__ __align__(16) uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 4];
     if (WIDE) bvh8_fill_order_lut(orderLut);
     if (WIDE) trace_persistent8(S.nodes8, S.tris8, count, head, refillBelow, leafMin, magic, orderLut, io);
     else trace_persistent(S.nodes, S.tris, count, head, refillBelow, leafMin, io);      // -DMRT_EXPERIMENTS builds only
@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(128, MINB) k_wf_trace(DeviceScene S, WfBuffers
     }
     WfIO io; io.P0 = b.P0; io.P1 = b.P1; io.S0 = b.S0; io.S1 = b.S1; io.H = b.H; io.visible = b.visible;
     io.qe = b.queueExt[parity]; io.qs = b.queueShadow[parity]; io.nExt = nExt;
-    __shared__ uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 1];
+    __shared__ __align__(16) uint8_t orderLut[WIDE ? MRT_ORDER_LUT_BYTES : 4];
     if (WIDE) bvh8_fill_order_lut(orderLut);
 #ifdef MRT_EXPERIMENTS
     __shared__ TqWarp tq[WIDE == 3 ? 4 : 1];

@@ -97,6 +97,7 @@ static void* worker_main(void* arg) {
         WCHECK(mrt_shard_layout(ctx, N, &rows_max, &shard_bytes));
         WCUDA(cudaMalloc(&send, shard_bytes));
         WCUDA(cudaMalloc(&recv, shard_bytes * N));
+        WNCCL(ncclAllGather(send, recv, 32, ncclFloat, w->comm, (cudaStream_t)stream));   /* untimed: NCCL sets its channels up on first use */
         WCHECK(mrt_sync(ctx));
         pthread_barrier_wait(w->barrier); w->passed = 1;
         WCHECK(mrt_event_record(ctx, 0));
@@ -114,6 +115,7 @@ static void* worker_main(void* arg) {
         const unsigned mine = o->frames > g ? (o->frames - g + N - 1) / N : 0;
         for (unsigned f = g >= 2 ? g - 2 : 0; f < g; ++f) WCHECK(mrt_set_noise(ctx, f % 3, w->tiles + (size_t)f * MRT_NOISE_TILE_FLOATS));
         WCUDA(cudaMalloc(&result, image_bytes));
+        WNCCL(ncclAllReduce(result, result, 32, ncclFloat, ncclSum, w->comm, (cudaStream_t)stream));   /* untimed: first-use set-up */
         WCHECK(mrt_sync(ctx));
         pthread_barrier_wait(w->barrier); w->passed = 1;
         WCHECK(mrt_event_record(ctx, 0));
