@@ -26,7 +26,9 @@ keep = ("gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio", "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio", "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio")
-commit = subprocess.run(["git", "-C", str(root), "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip() or "unknown"
+import os
+commit = subprocess.run(["git", "-C", str(root), "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip() \
+    or os.environ.get("MRT_COMMIT", "").strip() or ((root / "profiles" / "HEAD_COMMIT").read_text().strip() if (root / "profiles" / "HEAD_COMMIT").exists() else "unknown")
 dirty = subprocess.run(["git", "-C", str(root), "status", "--porcelain", "--", "metal-renderer_b200/csrc"], capture_output=True, text=True).stdout.strip()
 name = v[h.index("Kernel Name")] if "Kernel Name" in h else "?"
 out = [f"# ncu --set full --clock-control none --import-source on, one steady-state launch of {name}",
