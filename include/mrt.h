@@ -161,6 +161,13 @@ int mrt_set_noise(mrt_ctx* ctx, uint32_t slot, const float* tile);
 int mrt_set_row_shard(mrt_ctx* ctx, uint32_t first_row, uint32_t row_stride);
 int mrt_set_accumulate_mode(mrt_ctx* ctx, uint32_t mode);
 int mrt_set_pipeline(mrt_ctx* ctx, uint32_t pipeline);
+/* How the wavefront pipeline issues its waves (same kernels, same bits).  MRT_SCHEDULE_GRAPH (default): one CUDA graph per
+ * batch whose WHILE node repeats {trace, shade, trace, shade} until the trace kernel finds the batch finished — no empty
+ * launches, one cudaGraphLaunch from the host.  MRT_SCHEDULE_HOST_LOOP: the host launches the waves itself, at most 16
+ * ahead of the device, and stops when the trace kernel has flagged the end in a mapped host word; this is also what runs
+ * under MRT_PROFILE_TRACE_TIME, and what a kernel profiler needs (ncu cannot see kernel nodes of conditional graphs). */
+enum { MRT_SCHEDULE_GRAPH = 0, MRT_SCHEDULE_HOST_LOOP = 1 };
+int mrt_set_wave_schedule(mrt_ctx* ctx, uint32_t schedule);
 /* Profiling flags (OR them).  MRT_PROFILE_TRACE_TIME: bracket every trace-kernel launch of mrt_render_frames (wavefront
  * pipeline) with a CUDA event pair on the ctx stream, so that mrt_get_stats can report the dominant kernel's own device
  * time (costs two event records per wave).  MRT_PROFILE_VISITS: run the counting variant of the trace kernel, which adds

@@ -78,6 +78,7 @@ struct mrt_ctx {
     // arguments change (another size, frame count, shard, accumulate mode ...), replayed otherwise
     cudaGraphExec_t wfGraph = nullptr; std::string wfGraphKey;
     cudaStream_t captureStream = nullptr;                        // body of the WHILE node is captured on this one
+    uint32_t waveSchedule = MRT_SCHEDULE_GRAPH;                  // mrt_set_wave_schedule
     volatile unsigned int* hStop = nullptr; uint32_t batchSerial = 0;   // polling host loop: mapped word the trace kernel writes
     cudaEvent_t pollEvents[4] = {};                              // polling host loop: one event every 8 waves
     uint64_t graphKernels = 0; uint32_t kernelsPerWave = 2;      // kernels launched by graph replays (read back in mrt_get_stats)
@@ -491,6 +492,11 @@ int mrt_set_profile(mrt_ctx* c, uint32_t on) {
     c->countVisits = (on & MRT_PROFILE_VISITS) != 0;
     return MRT_OK;
 }
+int mrt_set_wave_schedule(mrt_ctx* c, uint32_t schedule) {
+    NEED(c && schedule <= MRT_SCHEDULE_HOST_LOOP, MRT_E_INVALID, "bad wave schedule");
+    c->waveSchedule = schedule;
+    return MRT_OK;
+}
 int mrt_set_pipeline(mrt_ctx* c, uint32_t pipeline) {
     NEED(c && pipeline <= MRT_PIPELINE_STAGED, MRT_E_INVALID, "bad pipeline");
     c->cfg.pipeline = pipeline;
@@ -631,7 +637,7 @@ static int render_wavefront(mrt_ctx* c, const RenderParams& p, uint32_t n_frames
     while (groups > 1 && b.slots / groups < 262144u) --groups;                     // small images: not worth splitting
     uint32_t per = ((b.slots + groups - 1u) / groups + 255u) / 256u * 256u;
     static const int graphEnv = env_knob("MRT_WF_GRAPH", 1);
-    const bool useGraph = graphEnv != 0 && !c->profile && groups == 1;
+    const bool useGraph = graphEnv != 0 && c->waveSchedule == MRT_SCHEDULE_GRAPH && !c->profile && groups == 1;
     const uint32_t perWave = 2u + (b.sortBits ? 1u : 0u);                            // kernels per wave: trace, shade (, sort)
     uint64_t launched = 0, pw = 0;
     c->kernelsPerWave = perWave;

@@ -2,7 +2,7 @@
 from ._lib import (ACCUM_MEAN, ACCUM_REPLACE, ACCUM_SUM, BUF_IMAGE, COMPARE_ABSOLUTE_VALUE, COMPARE_COLOR_TO_REF,
                    COMPARE_DISABLED, COMPARE_LUMINANCE, COMPARE_REF_TO_COLOR, BUF_INTERSECTIONS, BUF_LIGHT_RAYS, BUF_RAYS,
                    INTERSECTION, LIGHT_RAY, LIGHT_TRIANGLE, MATERIAL, NOISE_TILE_FLOATS, NOT_A_LIGHT, PIPELINE_AUTO,
-                   PIPELINE_MEGAKERNEL, PIPELINE_STAGED, PIPELINE_WAVEFRONT, PROFILE_TRACE_TIME, PROFILE_VISITS, RAY, TRIANGLE_REFERENCE, VERTEX, MrtError, lib)
+                   PIPELINE_MEGAKERNEL, PIPELINE_STAGED, PIPELINE_WAVEFRONT, PROFILE_TRACE_TIME, PROFILE_VISITS, RAY, SCHEDULE_GRAPH, SCHEDULE_HOST_LOOP, TRIANGLE_REFERENCE, VERTEX, MrtError, lib)
 from .renderer import Renderer
 from .scene import PROCEDURAL_SCENES, Scene, bvh_selftest, noise_tile, noise_tiles
 

@@ -34,6 +34,7 @@ MATERIAL_DIFFUSE, MATERIAL_MIRROR, MATERIAL_SMOOTH_PLASTIC, MATERIAL_SMOOTH_DIEL
 PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_STAGED = range(4)
 ACCUM_MEAN, ACCUM_SUM, ACCUM_REPLACE = range(3)
 COMPARE_DISABLED, COMPARE_ABSOLUTE_VALUE, COMPARE_REF_TO_COLOR, COMPARE_COLOR_TO_REF, COMPARE_LUMINANCE = range(5)   # Raytracing.h:27-31
+SCHEDULE_GRAPH, SCHEDULE_HOST_LOOP = 0, 1   # mrt_set_wave_schedule
 PROFILE_TRACE_TIME, PROFILE_VISITS = 1, 2      # mrt_set_profile flags (include/mrt.h)
 BUF_RAYS, BUF_LIGHT_RAYS, BUF_INTERSECTIONS, BUF_IMAGE = range(4)
 BUFFER_DTYPES = {BUF_RAYS: RAY, BUF_LIGHT_RAYS: LIGHT_RAY, BUF_INTERSECTIONS: INTERSECTION}
@@ -101,6 +102,7 @@ SIGNATURES = {
     "mrt_set_row_shard": (C.c_int, [_P, _U32, _U32]),
     "mrt_set_accumulate_mode": (C.c_int, [_P, _U32]),
     "mrt_set_pipeline": (C.c_int, [_P, _U32]),
+    "mrt_set_wave_schedule": (C.c_int, [_P, _U32]),
     "mrt_set_profile": (C.c_int, [_P, _U32]),
     "mrt_raygen": (C.c_int, [_P, _U32]),
     "mrt_intersect": (C.c_int, [_P, _U32]),

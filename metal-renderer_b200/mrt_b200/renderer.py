@@ -82,6 +82,10 @@ class Renderer:
         """flags: OR of PROFILE_TRACE_TIME (event pair per trace launch) and PROFILE_VISITS (node / triangle test counters)."""
         L.check(L.lib().mrt_set_profile(self._ctx, int(flags)))
 
+    def set_wave_schedule(self, schedule):
+        """SCHEDULE_GRAPH (default: one CUDA graph per batch, device-side stop) or SCHEDULE_HOST_LOOP."""
+        L.check(L.lib().mrt_set_wave_schedule(self._ctx, schedule))
+
     def set_pipeline(self, pipeline):
         L.check(L.lib().mrt_set_pipeline(self._ctx, pipeline))
 

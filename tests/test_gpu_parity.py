@@ -242,3 +242,25 @@ def test_visit_counters_leave_the_image_alone():
     assert s1["nodes_visited"] >= rays                       # every traced ray tests at least the root
     assert 0 < s1["triangles_tested"] < 64 * rays
     assert s1["profile_trace_launches"] > 0
+
+
+def test_host_loop_schedule_equals_the_graph_schedule_and_stops_early():
+    """mrt_set_wave_schedule: the WHILE graph and the polling host loop run the same kernels — same image, same ray
+    counts — and neither launches the static bound of frames * L + L + 2 waves when the paths die early."""
+    scene = m.Scene.procedural("cornell-water", 1)
+    w, h, frames, L = 320, 180, 24, 8
+    tiles = m.noise_tiles(11, 0, frames)
+    out = []
+    for schedule in (m.SCHEDULE_GRAPH, m.SCHEDULE_HOST_LOOP):
+        r, _ = setup_pair(scene, w, h, seed=11, max_path_length=L)
+        r.set_wave_schedule(schedule)
+        r.draw(frames, tiles)
+        st = r.stats()
+        out.append((r.save_current_image(), st))
+        waves, launches = st["waves_traced"], st["kernel_launches"]
+        assert 2 + 2 * waves <= launches, (schedule, waves, launches)
+        slack = 3 if schedule == m.SCHEDULE_GRAPH else 26            # graph: ends inside the wave pair; loop: polls every 8 waves, 16 ahead
+        assert launches <= 2 + 2 * (waves + slack), (schedule, waves, launches)
+        assert waves < frames * L + L + 2
+    assert_bits(out[0][0], out[1][0], "graph vs host loop")
+    assert (out[0][1]["primary_rays"], out[0][1]["shadow_rays"]) == (out[1][1]["primary_rays"], out[1][1]["shadow_rays"])
