@@ -271,6 +271,23 @@ int mrt_checkpoint_load(mrt_ctx* ctx, const char* path, uint32_t* frames_accumul
  * origin[3], minDistance, direction[3], maxDistance; `out` receives count intersections. */
 int mrt_intersect_host(mrt_ctx* ctx, const void* rays, size_t stride_bytes, uint32_t count,
                        mrt_intersection* out);
+/* mrt_intersect_host WITHOUT any device allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, same ray convention and the same results bit for bit; `rays` and `out` may be host or
+ * device pointers and are borrowed until the call returns (it synchronises the ctx stream).  The scratch
+ * mrt_intersect_host allocates per call (staged rays, hit records) and the traversal's work counter live in ONE static
+ * device array of MRT_NOALLOC_SCRATCH_BYTES (6 MiB + 256 B) that every GPU loading the library holds until the process
+ * exits; its device address is resolved once per device on the first call there (cudaGetSymbolAddress).  Limits:
+ * count <= MRT_NOALLOC_MAX_RAYS and stride_bytes <= MRT_NOALLOC_MAX_STRIDE, else MRT_E_INVALID with a message naming the
+ * limit.  The call issues cudaMemsetAsync / cudaMemcpyAsync / one kernel launch / cudaStreamSynchronize — no cudaMalloc,
+ * cudaFree or allocating library routine.  ALL calls on one device share the array and it keeps the last call's
+ * contents (the call clears the work counter itself): calls that overlap on the GPU — two contexts or two threads on
+ * the same device — RACE; serialise them. */
+#define MRT_NOALLOC_MAX_RAYS   65536u   /* rays per call */
+#define MRT_NOALLOC_MAX_STRIDE 80u      /* bytes per ray record (= sizeof(mrt_ray), the stride of Renderer.mm:519) */
+#define MRT_NOALLOC_SCRATCH_BYTES (256u + MRT_NOALLOC_MAX_RAYS * MRT_NOALLOC_MAX_STRIDE + MRT_NOALLOC_MAX_RAYS * 16u)
+int mrt_intersect_host_noalloc(mrt_ctx* ctx, const void* rays, size_t stride_bytes, uint32_t count,
+                               mrt_intersection* out);
 /* Same rays through an instrumented traversal; adds node/triangle visit counts to mrt_stats. */
 int mrt_profile_traversal(mrt_ctx* ctx, const void* rays, size_t stride_bytes, uint32_t count);
 

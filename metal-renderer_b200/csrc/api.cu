@@ -18,6 +18,7 @@
 #include "kernels.h"
 #include "mrt.h"
 #include "scene.h"
+#include "ctx_view.h"
 #include <nvtx3/nvToolsExt.h>       // header-only; ranges carry the reference's encoder labels (Renderer.mm:505, 527, 557, 574)
 
 using namespace mrt;
@@ -1225,3 +1226,18 @@ int mrt_bvh_selftest(const mrt_scene* s, uint32_t n_rays, uint64_t seed, mrt_bvh
 void mrt_noise_fill(uint64_t seed, uint32_t frame, float* tile) { noise_fill(seed, frame, tile); }
 
 }  // extern "C"
+
+// ---- internal: what csrc/noalloc.cu may see of a context (ctx_view.h) ------------------------------------------------
+namespace mrt {
+bool ctx_view(mrt_ctx* c, CtxView& out) {
+    if (!c) return false;
+    out.S = c->S; out.stream = c->stream; out.device = c->cfg.device; out.haveScene = c->haveScene;
+    out.kernelLaunches = &c->stats.kernel_launches;
+    return true;
+}
+int api_fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    return fail(code, "%s", buf);
+}
+}  // namespace mrt

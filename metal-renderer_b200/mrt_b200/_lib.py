@@ -35,6 +35,7 @@ PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_STAGED = range(
 ACCUM_MEAN, ACCUM_SUM, ACCUM_REPLACE = range(3)
 COMPARE_DISABLED, COMPARE_ABSOLUTE_VALUE, COMPARE_REF_TO_COLOR, COMPARE_COLOR_TO_REF, COMPARE_LUMINANCE = range(5)   # Raytracing.h:27-31
 SCHEDULE_GRAPH, SCHEDULE_HOST_LOOP = 0, 1   # mrt_set_wave_schedule
+NOALLOC_MAX_RAYS, NOALLOC_MAX_STRIDE = 65536, 80   # mrt_intersect_host_noalloc (include/mrt.h)
 PROFILE_TRACE_TIME, PROFILE_VISITS = 1, 2      # mrt_set_profile flags (include/mrt.h)
 BUF_RAYS, BUF_LIGHT_RAYS, BUF_INTERSECTIONS, BUF_IMAGE = range(4)
 BUFFER_DTYPES = {BUF_RAYS: RAY, BUF_LIGHT_RAYS: LIGHT_RAY, BUF_INTERSECTIONS: INTERSECTION}
@@ -133,6 +134,7 @@ SIGNATURES = {
     "mrt_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),
     "mrt_reset_stats": (C.c_int, [_P]),
     "mrt_intersect_host": (C.c_int, [_P, _P, _SZ, _U32, _P]),
+    "mrt_intersect_host_noalloc": (C.c_int, [_P, _P, _SZ, _U32, _P]),
     "mrt_profile_traversal": (C.c_int, [_P, _P, _SZ, _U32]),
     "mrt_scene_create_procedural": (C.c_int, [C.c_char_p, _U64, C.POINTER(_P)]),
     "mrt_scene_load_obj": (C.c_int, [C.c_char_p, C.POINTER(_P)]),

@@ -243,6 +243,16 @@ class Renderer:
         L.check(L.lib().mrt_intersect_host(self._ctx, L.ptr(rays), stride, count, L.ptr(out)))
         return out
 
+    def intersect_host_noalloc(self, rays, stride=None, out=None):
+        """intersect_host without any device allocation (static scratch array; <= NOALLOC_MAX_RAYS rays of stride
+        <= NOALLOC_MAX_STRIDE per call; calls that overlap on one GPU race)."""
+        rays = np.ascontiguousarray(rays)
+        stride = stride or rays.dtype.itemsize
+        count = rays.nbytes // stride
+        out = np.empty(count, dtype=L.INTERSECTION) if out is None else out
+        L.check(L.lib().mrt_intersect_host_noalloc(self._ctx, L.ptr(rays), stride, count, L.ptr(out)))
+        return out
+
     def profile_traversal(self, rays, stride=None):
         rays = np.ascontiguousarray(rays)
         stride = stride or rays.dtype.itemsize
