@@ -11,6 +11,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 #include "bvh.h"
 #include "bvh8.h"
@@ -280,9 +281,12 @@ int mrt_scene_prepare(const mrt_vertex* vertices, uint32_t vertex_count, const u
     mrt_prepared_scene* P = new (std::nothrow) mrt_prepared_scene();
     NEED(P, MRT_E_NOMEM, "out of host memory");
     if (bvh_max_leaf == 0) bvh_max_leaf = 4;
-    build_bvh(vertices, indices, triangle_count, bvh_max_leaf, bvh_threads, P->bvh);
+    {   // the binary tree (megakernel, mrt_intersect_host) is built beside the wide one: their serial parts overlap
+        std::thread binary([&] { build_bvh(vertices, indices, triangle_count, bvh_max_leaf, bvh_threads, P->bvh); });
+        build_bvh8(vertices, indices, triangle_count, bvh_threads, P->bvh8);
+        binary.join();
+    }
     if (!(P->bvh.depth < MRT_STACK_DEPTH_HOST)) { const uint32_t d = P->bvh.depth; delete P; return fail(MRT_E_INVALID, "BVH depth %u exceeds traversal stack", d); }
-    build_bvh8(vertices, indices, triangle_count, bvh_threads, P->bvh8);
     if (!(P->bvh8.depth + 2 < 32)) { const uint32_t d = P->bvh8.depth; delete P; return fail(MRT_E_INVALID, "wide BVH depth %u exceeds traversal stack", d); }
 
     // shading records: vertices gathered per triangle through TriangleReference.tri (Shaders.metal:129,140)

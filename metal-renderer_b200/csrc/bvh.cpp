@@ -19,6 +19,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <functional>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -38,9 +40,15 @@ struct BuildNode { Box box; uint32_t first, count, leftCount; };   // leftCount 
 constexpr int kMaxBins = 64;     // SAH bins per axis: Builder::bins, 4..kMaxBins (16 unless the caller says otherwise)
 constexpr uint32_t kParallelCutoff = 1u << 14;
 
+// One record per triangle, partitioned IN PLACE as the tree is built, so that every pass over a node's triangles is a
+// sequential read (with bounds kept aside and reached through an index array, the five passes per node were random
+// gathers: 430 ms of the 1 M-triangle front on 8 cores).  std::partition's swaps depend on the predicate values only, so
+// the resulting triangle order is the one the index array used to end up in.
+struct TriRef { float lo[3], hi[3]; uint32_t t; uint32_t pad; };
+
 struct Builder {
-    const float* tlo; const float* thi;          // per-triangle bounds, 3 floats each
-    std::vector<uint32_t> order;
+    std::vector<TriRef> refs;                    // per-triangle bounds + triangle index, in tree order when the build ends
+    std::vector<uint32_t> order;                 // refs[k].t, filled by build_front after the build (the emitters read it)
     std::vector<BuildNode> sparse;
     uint32_t maxLeaf;
     int bins = 16;
@@ -70,8 +78,9 @@ struct Builder {
             BuildNode& n = sparse[ni];
             n.first = first; n.count = count; n.leftCount = 0;
             Box b, cb; b.reset(); cb.reset();
+            const TriRef* ref = refs.data();
             for (uint32_t k = first; k < first + count; ++k) {
-                const float* l = tlo + 3 * size_t(order[k]); const float* h = thi + 3 * size_t(order[k]);
+                const float* l = ref[k].lo; const float* h = ref[k].hi;
                 b.grow(l, h);
                 float c[3] = {0.5f * (l[0] + h[0]), 0.5f * (l[1] + h[1]), 0.5f * (l[2] + h[2])};
                 cb.grow(c, c);
@@ -87,7 +96,7 @@ struct Builder {
                 Box bins[kMaxBins]; uint32_t cnt[kMaxBins];
                 for (int i = 0; i < kBins; ++i) { bins[i].reset(); cnt[i] = 0; }
                 for (uint32_t k = first; k < first + count; ++k) {
-                    const float* l = tlo + 3 * size_t(order[k]); const float* h = thi + 3 * size_t(order[k]);
+                    const float* l = ref[k].lo; const float* h = ref[k].hi;
                     int bi = std::min(kBins - 1, int((0.5f * (l[a] + h[a]) - cb.lo[a]) * scale));
                     bins[bi].grow(l, h); ++cnt[bi];
                 }
@@ -113,11 +122,10 @@ struct Builder {
                 mid = first + count / 2;           // identical centroids: split the list in half
             } else {
                 float scale = kBins / (cb.hi[bestAxis] - cb.lo[bestAxis]); float lo = cb.lo[bestAxis];
-                auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](uint32_t t) {
-                    const float* l = tlo + 3 * size_t(t); const float* h = thi + 3 * size_t(t);
-                    return std::min(kBins - 1, int((0.5f * (l[bestAxis] + h[bestAxis]) - lo) * scale)) <= bestBin;
+                auto it = std::partition(refs.begin() + first, refs.begin() + first + count, [&](const TriRef& r) {
+                    return std::min(kBins - 1, int((0.5f * (r.lo[bestAxis] + r.hi[bestAxis]) - lo) * scale)) <= bestBin;
                 });
-                mid = uint32_t(it - order.begin());
+                mid = uint32_t(it - refs.begin());
                 if (mid == first || mid == first + count) mid = first + count / 2;
             }
             uint32_t leftCount = mid - first, rightCount = count - leftCount;
@@ -159,9 +167,13 @@ static void build_front(const mrt_vertex* vertices, const uint32_t* indices, uin
     f.pad = 1e-5f * std::max(ext, mag) + 1e-30f;
     if (n == 0) return;
     Builder& b = f.b;
-    b.tlo = tlo.data(); b.thi = thi.data(); b.maxLeaf = maxLeaf; b.bins = bins < 4 ? 4 : (bins > kMaxBins ? kMaxBins : bins);
-    b.order.resize(n);
-    for (uint32_t t = 0; t < n; ++t) b.order[t] = t;
+    b.maxLeaf = maxLeaf; b.bins = bins < 4 ? 4 : (bins > kMaxBins ? kMaxBins : bins);
+    b.refs.resize(n);
+    for (uint32_t t = 0; t < n; ++t) {
+        TriRef& r = b.refs[t];
+        for (int a = 0; a < 3; ++a) { r.lo[a] = tlo[3 * size_t(t) + a]; r.hi[a] = thi[3 * size_t(t) + a]; }
+        r.t = t; r.pad = 0;
+    }
     b.sparse.resize(2 * size_t(n));
     b.parallel = threads > 1 && n >= 2 * kParallelCutoff;
     if (b.parallel) {
@@ -172,6 +184,9 @@ static void build_front(const mrt_vertex* vertices, const uint32_t* indices, uin
     } else {
         b.build(0, 0, n);
     }
+    b.order.resize(n);
+    for (uint32_t k = 0; k < n; ++k) b.order[k] = b.refs[k].t;
+    std::vector<TriRef>().swap(b.refs);
 }
 
 void build_bvh(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n, uint32_t maxLeaf, uint32_t threads,
@@ -270,12 +285,15 @@ static const uint32_t kMaxLeaf8 = getenv("MRT_BVH8_MAXLEAF") ? (uint32_t)std::mi
 struct Collapse {
     const Builder& b;
     float invRootArea;
-    std::vector<float> C;        // [node][i-1], i = 1..7
-    std::vector<uint8_t> K;      // [node][0] = 1: single child is a leaf; [node][j-1], j = 2..8: left share of distribute(j)
-    std::vector<uint8_t> U;      // bit i: C(n,i) comes from distribute(i) rather than from C(n,i-1)
+    // Tables over the sparse node array, left UNINITIALISED (74 MB at 1 M triangles: the zero fill alone was most of the
+    // collapse's time): combine() writes C[n][*] and K[n][0] of every node and K[n][1..7], U[n] of every inner node
+    // before anything reads them; leaves never have K[n][1..7] or U[n] read (collect() stops at a leaf first).
+    std::unique_ptr<float[]> C;  // [node][i-1], i = 1..7
+    std::unique_ptr<uint8_t[]> K;   // [node][0] = 1: single child is a leaf; [node][j-1], j = 2..8: left share of distribute(j)
+    std::unique_ptr<uint8_t[]> U;   // bit i: C(n,i) comes from distribute(i) rather than from C(n,i-1)
     explicit Collapse(const Builder& bb) : b(bb) {
         size_t m = bb.sparse.size();
-        C.assign(7 * m, 0.0f); K.assign(8 * m, 0); U.assign(m, 0);
+        C.reset(new float[7 * m]); K.reset(new uint8_t[8 * m]); U.reset(new uint8_t[m]);
         invRootArea = 1.0f / std::max(bb.sparse[0].box.half_area(), 1e-30f);
     }
     bool leaf(uint32_t n) const { return b.sparse[n].leftCount == 0; }
@@ -283,6 +301,19 @@ struct Collapse {
     uint32_t right(uint32_t n) const { return n + 2 * b.sparse[n].leftCount; }
 
     void solve(uint32_t n) {
+        if (!leaf(n)) { solve(left(n)); solve(right(n)); }
+        combine(n);
+    }
+    // The same over the subtrees in parallel: a node's table depends on its two children's only, so the result does
+    // not depend on how the recursion is cut into threads.  Subtrees below minCount triangles run serially.
+    void solve_parallel(uint32_t n, uint32_t minCount) {
+        if (leaf(n) || b.sparse[n].count < minCount) { solve(n); return; }
+        std::thread other([&] { solve_parallel(left(n), minCount); });
+        solve_parallel(right(n), minCount);
+        other.join();
+        combine(n);
+    }
+    void combine(uint32_t n) {
         const BuildNode& nd = b.sparse[n];
         const float A = nd.box.half_area() * invRootArea;
         float* c = &C[7 * size_t(n)]; uint8_t* k = &K[8 * size_t(n)];
@@ -292,7 +323,6 @@ struct Collapse {
             return;
         }
         const uint32_t l = left(n), r = right(n);
-        solve(l); solve(r);
         const float* cl = &C[7 * size_t(l)]; const float* cr = &C[7 * size_t(r)];
         float D[9];
         for (int j = 2; j <= 8; ++j) {
@@ -343,6 +373,12 @@ static void build_bvh8_bins(const mrt_vertex* vertices, const uint32_t* indices,
     // free to choose every leaf size from 1 to kMaxLeaf8 itself; 3 = stop at the binary builder's own SAH leaf rule.
     static const uint32_t frontLeaf = getenv("MRT_BVH8_FRONTLEAF") ? (uint32_t)std::min(3, std::max(1, atoi(getenv("MRT_BVH8_FRONTLEAF")))) : 1u;
     build_front(vertices, indices, n, frontLeaf, threads, front, bins);
+    static const bool verbose = getenv("MRT_BVH_VERBOSE") != nullptr;
+    auto lap = [&](const char* what) {
+        if (verbose) fprintf(stderr, "mrt: wide tree (%d bins): %-8s at %7.1f ms\n", bins, what,
+                             std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    };
+    lap("front");
     const Builder& b = front.b;
     const float pad = front.pad;
     auto finish = [&] { out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
@@ -352,111 +388,165 @@ static void build_bvh8_bins(const mrt_vertex* vertices, const uint32_t* indices,
         return;
     }
     Collapse col(b);
-    col.solve(0);
+    {
+        const uint32_t workers = threads ? threads : std::max(1u, std::thread::hardware_concurrency());
+        if (workers > 1 && n >= 4 * kParallelCutoff) col.solve_parallel(0, std::max(kParallelCutoff, n / (4 * workers)));
+        else col.solve(0);
+    }
+    lap("collapse");
     out.sah_cost = col.C[0];
     out.tris.reserve(n);
     out.nodes.reserve(size_t(n) / 4 + 16);
 
-    auto emit_tris = [&](const BuildNode& leaf) {
-        for (uint32_t k = leaf.first; k < leaf.first + leaf.count; ++k) {
+    // ---- emission, level by level (= the order of a breadth-first queue), every level in parallel ----
+    // A node's children get consecutive node indices in slot order and its leaf triangles consecutive records in slot
+    // order; the bases are running counts over the nodes in level order.  So a level is done in three steps: (1) in
+    // parallel, every node's children, padded boxes and slot assignment; (2) a serial prefix sum of inner-child and
+    // leaf-triangle counts; (3) in parallel, quantisation, the node record, its triangle records and the next level's
+    // items at their pre-assigned places.  The result does not depend on the number of threads.
+    if (threads == 0) threads = std::max(1u, std::thread::hardware_concurrency());
+    auto parallel_for = [&](size_t count, const std::function<void(size_t, size_t)>& body) {
+        const size_t workers = std::min<size_t>(threads, (count + 255) / 256);
+        if (workers <= 1) { body(0, count); return; }
+        std::vector<std::thread> pool;
+        for (size_t w = 0; w < workers; ++w) pool.emplace_back([&, w] { body(count * w / workers, count * (w + 1) / workers); });
+        for (auto& th : pool) th.join();
+    };
+    auto write_tris = [&](const BuildNode& leaf, BvhTri* dst) {
+        for (uint32_t k = leaf.first; k < leaf.first + leaf.count; ++k, ++dst) {
             uint32_t t = b.order[k];
             const float* V0 = vertices[indices[3 * size_t(t)]].v; const float* V1 = vertices[indices[3 * size_t(t) + 1]].v;
             const float* V2 = vertices[indices[3 * size_t(t) + 2]].v;
             BvhTri r;
             for (int a = 0; a < 3; ++a) { r.v2[a] = V2[a]; r.e1[a] = V0[a] - V2[a]; r.e2[a] = V1[a] - V2[a]; }
             r.index = t; r.pad1 = 0.0f; r.pad2 = 0.0f;
-            out.tris.push_back(r);
+            *dst = r;
         }
     };
 
-    struct Item { uint32_t bnode; uint32_t outIndex; uint32_t depth; bool wholeLeaf; };
-    std::deque<Item> queue;
-    out.nodes.push_back(Bvh8Node{});
-    queue.push_back(Item{0, 0, 1, col.is_leaf_child(0)});
-    while (!queue.empty()) {
-        Item it = queue.front(); queue.pop_front();
-        out.depth = std::max(out.depth, it.depth);
-        uint32_t kids[8]; int nk = 0;
-        if (it.wholeLeaf) { kids[0] = it.bnode; nk = 1; }          // only the root can be a bare leaf
-        else col.children_of(it.bnode, kids, nk);
-
-        // padded child boxes and their union
-        Box cb[8], nb; nb.reset();
-        for (int c = 0; c < nk; ++c) {
-            cb[c] = b.sparse[kids[c]].box;
-            for (int a = 0; a < 3; ++a) { cb[c].lo[a] -= pad; cb[c].hi[a] += pad; }
-            nb.grow(cb[c].lo, cb[c].hi);
-        }
-        // slot assignment: slot s (bit a set = +axis a) should hold the child lying furthest that way, so that
-        // visiting slots by descending (s ^ octInv) is roughly front to back for every ray octant
-        int slotOf[8]; bool slotUsed[8] = {}, kidDone[8] = {};
-        float score[8][8];
-        for (int c = 0; c < nk; ++c)
-            for (int s = 0; s < 8; ++s) {
-                float v = 0.0f;
+    struct Item { uint32_t bnode; uint32_t outIndex; bool wholeLeaf; };
+    struct Plan { uint32_t kids[8]; int nk; int kidAt[8]; Box cb[8]; Box nb; uint32_t inner, tris; uint32_t childBase, triBase; };
+    std::vector<Item> level, next;
+    std::vector<Plan> plans;
+    out.nodes.assign(1, Bvh8Node{});
+    out.tris.resize(n);                                  // every triangle is emitted exactly once
+    uint32_t triAt = 0;
+    level.push_back(Item{0, 0, col.is_leaf_child(0)});
+    uint32_t depth = 0;
+    while (!level.empty()) {
+        ++depth;
+        plans.resize(level.size());
+        parallel_for(level.size(), [&](size_t lo, size_t hi) {
+            for (size_t i = lo; i < hi; ++i) {
+                const Item& it = level[i];
+                Plan& P = plans[i];
+                P.nk = 0;
+                if (it.wholeLeaf) { P.kids[0] = it.bnode; P.nk = 1; }          // only the root can be a bare leaf
+                else col.children_of(it.bnode, P.kids, P.nk);
+                const int nk = P.nk;
+                // padded child boxes and their union
+                P.nb.reset();
+                for (int c = 0; c < nk; ++c) {
+                    P.cb[c] = b.sparse[P.kids[c]].box;
+                    for (int a = 0; a < 3; ++a) { P.cb[c].lo[a] -= pad; P.cb[c].hi[a] += pad; }
+                    P.nb.grow(P.cb[c].lo, P.cb[c].hi);
+                }
+                // slot assignment: slot s (bit a set = +axis a) should hold the child lying furthest that way, so that
+                // visiting slots by descending (s ^ octInv) is roughly front to back for every ray octant
+                int slotOf[8]; bool slotUsed[8] = {}, kidDone[8] = {};
+                float score[8][8];
+                for (int c = 0; c < nk; ++c)
+                    for (int s = 0; s < 8; ++s) {
+                        float v = 0.0f;
+                        for (int a = 0; a < 3; ++a) {
+                            float d = 0.5f * (P.cb[c].lo[a] + P.cb[c].hi[a]) - 0.5f * (P.nb.lo[a] + P.nb.hi[a]);
+                            v += ((s >> a) & 1) ? d : -d;
+                        }
+                        score[c][s] = v;
+                    }
+                for (int r = 0; r < nk; ++r) {
+                    int bc = -1, bs = -1; float bv = -FLT_MAX;
+                    for (int c = 0; c < nk; ++c) if (!kidDone[c])
+                        for (int s = 0; s < 8; ++s) if (!slotUsed[s] && (bc < 0 || score[c][s] > bv)) { bv = score[c][s]; bc = c; bs = s; }
+                    slotOf[bc] = bs; kidDone[bc] = true; slotUsed[bs] = true;
+                }
+                for (int s = 0; s < 8; ++s) P.kidAt[s] = -1;
+                for (int c = 0; c < nk; ++c) P.kidAt[slotOf[c]] = c;
+                P.inner = 0; P.tris = 0;
+                for (int c = 0; c < nk; ++c) {
+                    if (col.is_leaf_child(P.kids[c])) P.tris += b.sparse[P.kids[c]].count; else ++P.inner;
+                }
+            }
+        });
+        uint32_t nodeAt = uint32_t(out.nodes.size());
+        const uint32_t nodeStart = nodeAt;
+        for (Plan& P : plans) { P.childBase = nodeAt; P.triBase = triAt; nodeAt += P.inner; triAt += P.tris; }
+        out.nodes.resize(nodeAt);
+        next.resize(nodeAt - nodeStart);
+        parallel_for(level.size(), [&](size_t lo, size_t hi) {
+            for (size_t i = lo; i < hi; ++i) {
+                const Plan& P = plans[i];
+                const int nk = P.nk;
+                Bvh8Node nd{};
+                for (int a = 0; a < 3; ++a) nd.p[a] = P.nb.lo[a];
+                // per-axis power-of-two grid step with 255 * step >= extent; planes rounded outwards
                 for (int a = 0; a < 3; ++a) {
-                    float d = 0.5f * (cb[c].lo[a] + cb[c].hi[a]) - 0.5f * (nb.lo[a] + nb.hi[a]);
-                    v += ((s >> a) & 1) ? d : -d;
+                    double ext = double(P.nb.hi[a]) - double(P.nb.lo[a]);
+                    int ex = 0;
+                    std::frexp(std::max(ext, 1e-37) / 255.0, &ex);
+                    for (;; ++ex) {
+                        if (ex < -126) ex = -126;
+                        const double step = std::ldexp(1.0, ex);
+                        bool ok = true;
+                        for (int c = 0; c < nk && ok; ++c) {
+                            double qh = std::ceil((double(P.cb[c].hi[a]) - double(nd.p[a])) / step);
+                            if (qh > 255.0) ok = false;
+                        }
+                        if (ok || ex >= 127) break;
+                    }
+                    nd.e[a] = uint8_t(ex + 127);
+                    const double step = std::ldexp(1.0, ex);
+                    for (int s = 0; s < 8; ++s) {
+                        int c = P.kidAt[s];
+                        if (c < 0) { nd.qlo[a][s] = 255; nd.qhi[a][s] = 0; continue; }      // empty slot: inverted box
+                        double ql = std::floor((double(P.cb[c].lo[a]) - double(nd.p[a])) / step);
+                        double qh = std::ceil((double(P.cb[c].hi[a]) - double(nd.p[a])) / step);
+                        nd.qlo[a][s] = uint8_t(std::min(255.0, std::max(0.0, ql)));
+                        nd.qhi[a][s] = uint8_t(std::min(255.0, std::max(0.0, qh)));
+                    }
                 }
-                score[c][s] = v;
-            }
-        for (int r = 0; r < nk; ++r) {
-            int bc = -1, bs = -1; float bv = -FLT_MAX;
-            for (int c = 0; c < nk; ++c) if (!kidDone[c])
-                for (int s = 0; s < 8; ++s) if (!slotUsed[s] && (bc < 0 || score[c][s] > bv)) { bv = score[c][s]; bc = c; bs = s; }
-            slotOf[bc] = bs; kidDone[bc] = true; slotUsed[bs] = true;
-        }
-        int kidAt[8]; for (int s = 0; s < 8; ++s) kidAt[s] = -1;
-        for (int c = 0; c < nk; ++c) kidAt[slotOf[c]] = c;
-
-        Bvh8Node nd{};
-        for (int a = 0; a < 3; ++a) nd.p[a] = nb.lo[a];
-        // per-axis power-of-two grid step with 255 * step >= extent; planes rounded outwards
-        for (int a = 0; a < 3; ++a) {
-            double ext = double(nb.hi[a]) - double(nb.lo[a]);
-            int ex = 0;
-            std::frexp(std::max(ext, 1e-37) / 255.0, &ex);
-            for (;; ++ex) {
-                if (ex < -126) ex = -126;
-                const double step = std::ldexp(1.0, ex);
-                bool ok = true;
-                for (int c = 0; c < nk && ok; ++c) {
-                    double qh = std::ceil((double(cb[c].hi[a]) - double(nd.p[a])) / step);
-                    if (qh > 255.0) ok = false;
+                // children: inner ones get consecutive node indices in slot order, leaf triangles consecutive records
+                nd.childBase = P.childBase;
+                nd.triBase = P.triBase;
+                uint32_t triOffset = 0, innerRank = 0;
+                for (int s = 0; s < 8; ++s) {
+                    int c = P.kidAt[s];
+                    if (c < 0) continue;
+                    const BuildNode& ch = b.sparse[P.kids[c]];
+                    if (col.is_leaf_child(P.kids[c])) {
+                        nd.leafTris |= ((1u << ch.count) - 1u) << (3 * s);                     // unary count at the slot's three bits
+                        write_tris(ch, out.tris.data() + P.triBase + triOffset);
+                        triOffset += ch.count;
+                    } else {
+                        nd.imask |= uint8_t(1u << s);
+                        const uint32_t idx = P.childBase + innerRank++;
+                        next[idx - nodeStart] = Item{P.kids[c], idx, false};
+                    }
                 }
-                if (ok || ex >= 127) break;
+                out.nodes[level[i].outIndex] = nd;
             }
-            nd.e[a] = uint8_t(ex + 127);
-            const double step = std::ldexp(1.0, ex);
-            for (int s = 0; s < 8; ++s) {
-                int c = kidAt[s];
-                if (c < 0) { nd.qlo[a][s] = 255; nd.qhi[a][s] = 0; continue; }      // empty slot: inverted box
-                double ql = std::floor((double(cb[c].lo[a]) - double(nd.p[a])) / step);
-                double qh = std::ceil((double(cb[c].hi[a]) - double(nd.p[a])) / step);
-                nd.qlo[a][s] = uint8_t(std::min(255.0, std::max(0.0, ql)));
-                nd.qhi[a][s] = uint8_t(std::min(255.0, std::max(0.0, qh)));
-            }
-        }
-        // children: inner ones get consecutive node indices in slot order, leaf triangles consecutive records
-        nd.childBase = uint32_t(out.nodes.size());
-        nd.triBase = uint32_t(out.tris.size());
-        uint32_t triOffset = 0;
-        for (int s = 0; s < 8; ++s) {
-            int c = kidAt[s];
-            if (c < 0) continue;
-            const BuildNode& ch = b.sparse[kids[c]];
-            if (col.is_leaf_child(kids[c])) {
-                nd.leafTris |= ((1u << ch.count) - 1u) << (3 * s);                     // unary count at the slot's three bits
-                emit_tris(ch);
-                triOffset += ch.count;
-            } else {
-                nd.imask |= uint8_t(1u << s);
-                uint32_t idx = uint32_t(out.nodes.size());
-                out.nodes.push_back(Bvh8Node{});
-                queue.push_back(Item{kids[c], idx, it.depth + 1, false});
-            }
-        }
-        out.nodes[it.outIndex] = nd;
+        });
+        level.swap(next);
+        next.clear();
+    }
+    out.depth = depth;
+    lap("emit");
+    if (verbose) {                      // FNV-1a over the emitted arrays: the tree must not depend on the thread count
+        auto fnv = [](const void* p, size_t bytes) { uint64_t h = 1469598103934665603ull; const unsigned char* c = (const unsigned char*)p;
+                                                     for (size_t i = 0; i < bytes; ++i) { h ^= c[i]; h *= 1099511628211ull; } return h; };
+        fprintf(stderr, "mrt: wide tree (%d bins): %zu nodes %016llx, %zu triangle records %016llx, depth %u\n", bins, out.nodes.size(),
+                (unsigned long long)fnv(out.nodes.data(), out.nodes.size() * sizeof(Bvh8Node)), out.tris.size(),
+                (unsigned long long)fnv(out.tris.data(), out.tris.size() * sizeof(BvhTri)), out.depth);
     }
     finish();
 }
@@ -600,16 +690,23 @@ void build_bvh8(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n,
         const float* v = vertices[indices[t]].v;
         for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], v[a]); hi[a] = std::max(hi[a], v[a]); }
     }
-    double bestCost = 0.0;
+    // every candidate is built with all threads; its (single-threaded) sampling runs beside the next candidate's build
+    std::vector<Bvh8Result> trees(cand.size());
+    std::vector<double> costs(cand.size(), 0.0);
+    std::vector<std::thread> samplers;
     for (size_t i = 0; i < cand.size(); ++i) {
-        Bvh8Result r;
-        build_bvh8_bins(vertices, indices, n, threads, cand[i], r);
-        const double cost = bvh8_sample_cost(r, lo, hi, 4096, 4, 0x5EEDull);
-        if (getenv("MRT_BVH_VERBOSE")) fprintf(stderr, "mrt: wide tree with %d SAH bins: %zu nodes, sampled cost %.3f per ray\n", cand[i], r.nodes.size(), cost);
+        build_bvh8_bins(vertices, indices, n, threads, cand[i], trees[i]);
+        samplers.emplace_back([&, i] { costs[i] = bvh8_sample_cost(trees[i], lo, hi, 4096, 4, 0x5EEDull); });
+    }
+    for (auto& t : samplers) t.join();
+    double bestCost = 0.0; size_t best = 0;
+    for (size_t i = 0; i < cand.size(); ++i) {
+        if (getenv("MRT_BVH_VERBOSE")) fprintf(stderr, "mrt: wide tree with %d SAH bins: %zu nodes, sampled cost %.3f per ray\n", cand[i], trees[i].nodes.size(), costs[i]);
         // the first candidate stays unless another one is at least 2 % cheaper: below that the sample does not decide
         // (1M-triangle lattice: 64 bins 0.5 % cheaper on the sample, 4 % slower on the GPU)
-        if (i == 0 || cost < 0.98 * bestCost) { bestCost = cost; out = std::move(r); }
+        if (i == 0 || costs[i] < 0.98 * bestCost) { bestCost = costs[i]; best = i; }
     }
+    out = std::move(trees[best]);
     out.sample_cost = (float)bestCost;
     out.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }

@@ -52,3 +52,30 @@ def test_prepare_rejects_out_of_range_indices():
     lights = s.lights.copy(); lights["index"][0] = s.triangle_count
     rc, msg = prepare(s, lights=lights)
     assert rc == -1 and "light 0" in msg
+
+
+def test_wide_tree_does_not_depend_on_the_thread_count():
+    """The host build is parallel in its front, collapse and emission; the emitted nodes and triangle records (FNV hashes
+    printed under MRT_BVH_VERBOSE) must be the same for 1 thread, 3 threads and all cores."""
+    import os, pathlib, re, subprocess, sys
+    root = pathlib.Path(__file__).resolve().parent.parent
+    script = r"""
+import sys, ctypes as C
+sys.path[:0] = [%r]
+import mrt_b200 as m
+from mrt_b200 import _lib as L
+s = m.Scene.procedural("spheres-64k", 3)
+out = C.c_void_p()
+rc = L.lib().mrt_scene_prepare(L.ptr(s.vertices), len(s.vertices), L.ptr(s.indices), len(s.references), L.ptr(s.references),
+                               L.ptr(s.materials), len(s.materials), L.ptr(s.lights), s.light_count, 4, int(sys.argv[1]), C.byref(out))
+assert rc == 0
+""" % str(root / "metal-renderer_b200")
+    seen = []
+    for threads in (1, 3, 0):
+        run = subprocess.run([sys.executable, "-c", script, str(threads)], env=dict(os.environ, MRT_BVH_VERBOSE="1"),
+                             capture_output=True, text=True, timeout=300)
+        assert run.returncode == 0, run.stderr[-1500:]
+        hashes = re.findall(r"\((\d+) bins\): (\d+) nodes ([0-9a-f]{16}), (\d+) triangle records ([0-9a-f]{16}), depth (\d+)", run.stderr)
+        assert len(hashes) == 2, run.stderr[-1500:]                    # the two SAH-bin candidates
+        seen.append(hashes)
+    assert seen[0] == seen[1] == seen[2], seen
