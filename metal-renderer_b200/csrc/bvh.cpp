@@ -690,15 +690,18 @@ void build_bvh8(const mrt_vertex* vertices, const uint32_t* indices, uint32_t n,
         const float* v = vertices[indices[t]].v;
         for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], v[a]); hi[a] = std::max(hi[a], v[a]); }
     }
-    // every candidate is built with all threads; its (single-threaded) sampling runs beside the next candidate's build
+    // the candidates are built and sampled side by side, each with its own worker threads: the serial stretches of one
+    // (the top of its front, where one thread bins all the triangles; the prefix sums; the ray sample) run while the
+    // other's workers are busy.  Each build is deterministic on its own, so the outcome is the same as one after the other.
     std::vector<Bvh8Result> trees(cand.size());
     std::vector<double> costs(cand.size(), 0.0);
-    std::vector<std::thread> samplers;
-    for (size_t i = 0; i < cand.size(); ++i) {
-        build_bvh8_bins(vertices, indices, n, threads, cand[i], trees[i]);
-        samplers.emplace_back([&, i] { costs[i] = bvh8_sample_cost(trees[i], lo, hi, 4096, 4, 0x5EEDull); });
-    }
-    for (auto& t : samplers) t.join();
+    std::vector<std::thread> builders;
+    for (size_t i = 0; i < cand.size(); ++i)
+        builders.emplace_back([&, i] {
+            build_bvh8_bins(vertices, indices, n, threads, cand[i], trees[i]);
+            costs[i] = bvh8_sample_cost(trees[i], lo, hi, 4096, 4, 0x5EEDull);
+        });
+    for (auto& t : builders) t.join();
     double bestCost = 0.0; size_t best = 0;
     for (size_t i = 0; i < cand.size(); ++i) {
         if (getenv("MRT_BVH_VERBOSE")) fprintf(stderr, "mrt: wide tree with %d SAH bins: %zu nodes, sampled cost %.3f per ray\n", cand[i], trees[i].nodes.size(), costs[i]);
