@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define MRT_VERSION 101
+#define MRT_VERSION 102
 
 enum {
     MRT_OK = 0,
@@ -168,6 +168,28 @@ int mrt_set_pipeline(mrt_ctx* ctx, uint32_t pipeline);
  * under MRT_PROFILE_TRACE_TIME, and what a kernel profiler needs (ncu cannot see kernel nodes of conditional graphs). */
 enum { MRT_SCHEDULE_GRAPH = 0, MRT_SCHEDULE_HOST_LOOP = 1 };
 int mrt_set_wave_schedule(mrt_ctx* ctx, uint32_t schedule);
+
+/* ---- optics extension: SURVEY.md 8(f4), BEYOND THE REFERENCE ------------------------------------------------------------
+ * Nothing here has a counterpart in the reference, so nothing here can be pinned against it: the checker is the same
+ * algorithm restated in oracle/ (bit-exact against the CUDA path) plus closed forms (Snell's law through a slab, total
+ * internal reflection, the alias table's marginals).  flags = 0 (the default) is the reference's behaviour bit for bit
+ * and launches the same kernels as before; any other value launches separate instantiations of the shade kernels.
+ *   MRT_EXT_REFRACTION   smooth dielectrics refract by Snell's law instead of continuing straight through
+ *                        (KernelHelpers.h:151-166 keeps wO = wI): side from the sign of n.wI, total internal reflection,
+ *                        both lobes weigh 1, radiance scaled by (etaI/etaT)^2 on transmission, the continued path and
+ *                        its light-sampling ray start on the side the path leaves on.  No nested media.
+ *   MRT_EXT_DISPERSION   (needs REFRACTION) the index of refraction of channel c in {0,1,2} is material.ior +
+ *                        dispersion * (c - 1); a path entering a medium keeps ONE live channel (uniform choice, weight =
+ *                        number of live channels).  The 3 channels are Spectrum.h:3's SPECTRUM_SAMPLES; more samples
+ *                        than 3 would change every ABI struct that embeds a Spectrum and is NOT built.
+ *   MRT_EXT_ALIAS_LIGHTS light triangles are selected through a Walker/Vose alias table of the same pdfs (2 loads)
+ *                        instead of the CDF search of KernelHelpers.h:49-54; same expectation, different samples.
+ * Wavefront and staged pipelines; MRT_E_STATE under MRT_PIPELINE_MEGAKERNEL. */
+enum { MRT_EXT_REFRACTION = 1, MRT_EXT_DISPERSION = 2, MRT_EXT_ALIAS_LIGHTS = 4 };
+int mrt_set_extensions(mrt_ctx* ctx, uint32_t flags, float dispersion);
+/* The alias table mrt_set_scene builds from the light pdfs (host code, no GPU): slot i keeps itself when the fraction
+ * is below prob[i], else yields alias[i]. */
+int mrt_build_alias_table(const float* pdf, uint32_t count, float* prob, uint32_t* alias);
 /* Profiling flags (OR them).  MRT_PROFILE_TRACE_TIME: bracket every trace-kernel launch of mrt_render_frames (wavefront
  * pipeline) with a CUDA event pair on the ctx stream, so that mrt_get_stats can report the dominant kernel's own device
  * time (costs two event records per wave).  MRT_PROFILE_VISITS: run the counting variant of the trace kernel, which adds

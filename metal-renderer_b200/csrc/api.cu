@@ -248,11 +248,36 @@ static cudaError_t set_l2_window(mrt_ctx* c, void* base, size_t bytes) {
 
 // Host half of -initRaytracing (Renderer.mm:450-469): validation, both trees, records repacked for 128-bit loads.
 // Built once, uploaded to any number of contexts (one per GPU) by mrt_set_prepared_scene.
+// Walker/Vose alias table of n probabilities (optics extension, MRT_EXT_ALIAS_LIGHTS): slot i keeps itself with
+// probability prob[i] and hands the rest to alias[i], so that P(i) = (prob[i] + sum over slots j with alias[j] == i of
+// (1 - prob[j])) / n = pdf[i] / sum(pdf).  Worked in double, small / large work lists in index order: deterministic.
+static void build_alias_table(const float* pdf, uint32_t n, float* prob, uint32_t* alias) {
+    if (n == 0) return;
+    double total = 0.0;
+    for (uint32_t i = 0; i < n; ++i) total += pdf[i] > 0.0f ? (double)pdf[i] : 0.0;
+    std::vector<double> q(n);
+    std::vector<uint32_t> small, large;
+    for (uint32_t i = 0; i < n; ++i) {
+        q[i] = total > 0.0 ? (pdf[i] > 0.0f ? (double)pdf[i] : 0.0) * n / total : 1.0;
+        alias[i] = i;
+        (q[i] < 1.0 ? small : large).push_back(i);
+    }
+    size_t si = 0, li = 0;
+    while (si < small.size() && li < large.size()) {
+        const uint32_t sm = small[si++], lg = large[li];
+        prob[sm] = (float)q[sm]; alias[sm] = lg;
+        q[lg] -= 1.0 - q[sm];
+        if (q[lg] < 1.0) { small.push_back(lg); ++li; }
+    }
+    for (; li < large.size(); ++li) prob[large[li]] = 1.0f;
+    for (; si < small.size(); ++si) prob[small[si]] = 1.0f;        // rounding leftovers
+}
+
 struct mrt_prepared_scene {
     BvhResult bvh; Bvh8Result bvh8;
     std::vector<float> shade, mats, lts;
     std::vector<uint32_t> cdfAndGuide, triSlotWide, triSlotBinary;
-    uint32_t cdfCount = 0, guideBuckets = 0, lightCount = 0, triangleCount = 0;
+    uint32_t cdfCount = 0, guideBuckets = 0, aliasOffset = 0, lightCount = 0, triangleCount = 0;
     float lo[3] = {0, 0, 0}, hi[3] = {1, 1, 1};
 };
 
@@ -325,6 +350,18 @@ int mrt_scene_prepare(const mrt_vertex* vertices, uint32_t vertex_count, const u
     std::memcpy(P->cdfAndGuide.data(), cdf.data(), cdf.size() * 4);
     if (!guide.empty()) std::memcpy(P->cdfAndGuide.data() + cdf.size(), guide.data(), guide.size() * 4);
     P->cdfCount = (uint32_t)cdf.size(); P->guideBuckets = buckets;
+    {   // alias table of the same pdfs, 8-byte aligned behind cdf and guide: (prob, alias) per light
+        P->aliasOffset = (uint32_t)((P->cdfAndGuide.size() + 1u) & ~size_t(1));
+        P->cdfAndGuide.resize(P->aliasOffset + 2 * (size_t)light_count, 0u);
+        std::vector<float> pdf(light_count), prob(light_count);
+        std::vector<uint32_t> alias(light_count);
+        for (uint32_t l = 0; l < light_count; ++l) pdf[l] = lights[l].pdf;
+        build_alias_table(pdf.data(), light_count, prob.data(), alias.data());
+        for (uint32_t l = 0; l < light_count; ++l) {
+            std::memcpy(&P->cdfAndGuide[P->aliasOffset + 2 * (size_t)l], &prob[l], 4);
+            P->cdfAndGuide[P->aliasOffset + 2 * (size_t)l + 1] = alias[l];
+        }
+    }
     P->triSlotWide.assign(std::max(1u, triangle_count), 0u);
     for (size_t k = 0; k < P->bvh8.tris.size(); ++k) P->triSlotWide[P->bvh8.tris[k].index] = (uint32_t)k;
     P->triSlotBinary.assign(std::max(1u, triangle_count), 0u);
@@ -361,6 +398,7 @@ int mrt_set_prepared_scene(mrt_ctx* c, const mrt_prepared_scene* P) {
     CK(upload(&c->dCdf, P->cdfAndGuide.data(), P->cdfAndGuide.size() * 4));
     c->S.lightGuide = P->guideBuckets ? reinterpret_cast<const uint32_t*>(c->dCdf) + P->cdfCount : nullptr;
     c->S.lightGuideBuckets = P->guideBuckets;
+    c->S.lightAlias = reinterpret_cast<const float2*>(reinterpret_cast<const uint32_t*>(c->dCdf) + P->aliasOffset);
     {   // wide nodes and their triangle records share ONE allocation (nodes first), so that a single L2 access-policy
         // window can cover what the trace kernel gathers from
         const size_t nodeBytes = (bvh8.nodes.size() * sizeof(Bvh8Node) + 255) & ~size_t(255);
@@ -500,6 +538,19 @@ int mrt_set_profile(mrt_ctx* c, uint32_t on) {
 int mrt_set_wave_schedule(mrt_ctx* c, uint32_t schedule) {
     NEED(c && schedule <= MRT_SCHEDULE_HOST_LOOP, MRT_E_INVALID, "bad wave schedule");
     c->waveSchedule = schedule;
+    return MRT_OK;
+}
+int mrt_set_extensions(mrt_ctx* c, uint32_t flags, float dispersion) {
+    NEED(c, MRT_E_INVALID, "ctx is NULL");
+    NEED((flags & ~(uint32_t)(MRT_EXT_REFRACTION | MRT_EXT_DISPERSION | MRT_EXT_ALIAS_LIGHTS)) == 0, MRT_E_INVALID, "unknown extension bit in 0x%x", flags);
+    NEED(!(flags & MRT_EXT_DISPERSION) || (flags & MRT_EXT_REFRACTION), MRT_E_INVALID, "MRT_EXT_DISPERSION needs MRT_EXT_REFRACTION");
+    NEED(std::isfinite(dispersion) && std::fabs(dispersion) <= 0.5f, MRT_E_INVALID, "dispersion %g outside [-0.5, 0.5]", (double)dispersion);
+    c->S.extFlags = flags; c->S.dispersion = (flags & MRT_EXT_DISPERSION) ? dispersion : 0.0f;
+    return MRT_OK;
+}
+int mrt_build_alias_table(const float* pdf, uint32_t count, float* prob, uint32_t* alias) {
+    if (!pdf || !prob || !alias) return MRT_E_INVALID;
+    build_alias_table(pdf, count, prob, alias);
     return MRT_OK;
 }
 int mrt_set_pipeline(mrt_ctx* c, uint32_t pipeline) {
@@ -840,6 +891,7 @@ int mrt_render_frames(mrt_ctx* c, uint32_t first_frame, uint32_t n_frames, uint3
         p.counters = c->cfg.count_rays ? c->dCounters : nullptr;
         CK(cudaEventRecord(c->evK0, c->stream));
         if (c->cfg.pipeline == MRT_PIPELINE_MEGAKERNEL) {
+            NEED(c->S.extFlags == 0, MRT_E_STATE, "the optics extension (mrt_set_extensions) runs on the wavefront and staged pipelines only");
             p.counters = c->dCounters;
             launch_render_fused(c->stream, p, c->cfg.count_rays != 0);
             LAUNCHED(c, 1);

@@ -25,6 +25,10 @@ struct DeviceScene {
     uint32_t lightGuideBuckets; // power of two, 0 = no table (few lights)
     uint32_t lightCount;
     uint32_t triangleCount;
+    // optics extension (NOT in the reference, off by default — see mrt_set_extensions in mrt.h)
+    const float2* lightAlias;   // per light triangle: (threshold, alias index as bits) — Walker/Vose table of the light pdfs
+    uint32_t extFlags;          // MRT_EXT_* bits; 0 = the reference's behaviour, the EXT kernel variants are never launched
+    float dispersion;           // MRT_EXT_DISPERSION: ior of channel c = material.ior + dispersion * (c - 1)
 };
 
 struct Vtx { f3 v, n; };
@@ -150,6 +154,66 @@ __device__ __forceinline__ uint32_t selectLightTriangle(float xi, const float* c
     }
     return lo;
 }
+// ---- optics extension (no counterpart in the reference; restated in oracle/orc_shading.h under the same names) -----
+// Walker/Vose alias selection with ONE uniform number: slot = floor(xi * n), the fraction decides slot vs its alias.
+// Selects light i with probability pdf[i] (the table is built from the same pdfs, scene.cpp build_alias_table), in two
+// dependent loads whatever the number of lights; the index differs from the CDF inversion's, so images differ sample by
+// sample and agree in expectation.  Never returns the sentinel.
+__device__ __forceinline__ uint32_t selectLightAlias(float xi, const float2* table, uint32_t trianglesCount) {
+    if (trianglesCount == 0u) return 0u;
+    const float s = fminf(fmaxf(xi, 0.0f), 1.0f) * float(trianglesCount);
+    const uint32_t slot = min(uint32_t(s), trianglesCount - 1u);
+    const float2 e = __ldg(table + slot);
+    return (s - float(slot)) < e.x ? slot : __float_as_uint(e.y);
+}
+// Smooth dielectric with Snell refraction.  The reference's branch (KernelHelpers.h:151-166) continues straight through
+// and keeps a cosine on the reflected lobe; here: the side is taken from the sign of n.wI (n is the outward shading
+// normal), the far side's index is the material's when entering and air's (the generator's 1.00029, Shaders.metal:99) when
+// leaving, the near side's is the one the ray carries (Ray.params.w), total internal reflection reflects, both lobes are
+// delta lobes with bsdf/pdf = 1 and the transmitted radiance is scaled by (etaI/etaT)^2 (radiance transport from the
+// camera).  No stack of nested media.  Dispersion: a transmitted path entering the medium keeps ONE of its live
+// throughput channels (chosen uniformly with noise.x, weight = number of live channels) and refracts with that channel's
+// index; it carries that index until it leaves.  `channelScale` multiplies the throughput.
+#define MRT_AIR_IOR 1.00029f
+__device__ __forceinline__ f3 refractiveBounce(const Mat& material, const DeviceScene& S, f3 wI, float rayIor, f3 throughput, f3 n,
+                                               float4 noiseSample, float& bsdf, float& pdf, float& ior, f3& channelScale) {
+    const float cosN = dot(n, -wI);
+    const bool entering = cosN > 0.0f;
+    const f3 nn = entering ? n : -n;
+    const float etaI = rayIor;
+    float etaT = entering ? material.ior : MRT_AIR_IOR;
+    const float fI = fresnel(nn, -wI, etaI, etaT);
+    channelScale = mk3(1.0f, 1.0f, 1.0f);
+    ior = rayIor;
+    if (fI < noiseSample.y) {
+        if (entering && (S.extFlags & MRT_EXT_DISPERSION) && S.dispersion != 0.0f) {
+            const bool a0 = throughput.x != 0.0f, a1 = throughput.y != 0.0f, a2 = throughput.z != 0.0f;
+            const uint32_t k = uint32_t(a0) + uint32_t(a1) + uint32_t(a2);
+            if (k > 0u) {
+                const uint32_t rank = min(uint32_t(noiseSample.x * float(k)), k - 1u);   // the rank-th live channel
+                uint32_t seen = 0u, c = 3u;
+                if (a0) { if (seen == rank) c = 0u; ++seen; }
+                if (a1) { if (seen == rank && c == 3u) c = 1u; ++seen; }
+                if (a2) { if (seen == rank && c == 3u) c = 2u; ++seen; }
+                const float w = float(k);
+                channelScale = mk3(c == 0u ? w : 0.0f, c == 1u ? w : 0.0f, c == 2u ? w : 0.0f);
+                etaT = material.ior + S.dispersion * (float(c) - 1.0f);
+            }
+        }
+        const float eta = __fdiv_rn(etaI, etaT);
+        const float cosI = clampf(dot(nn, -wI), 0.0f, 1.0f);
+        const float sin2T = (eta * eta) * (1.0f - cosI * cosI);
+        if (sin2T < 1.0f) {
+            const float cosT = __fsqrt_rn(1.0f - sin2T);
+            ior = etaT; bsdf = eta * eta; pdf = 1.0f;
+            return normalize(wI * eta + nn * (eta * cosI - cosT));
+        }
+        channelScale = mk3(1.0f, 1.0f, 1.0f);       // this channel is totally reflected: no selection was needed
+    }
+    bsdf = 1.0f; pdf = 1.0f;
+    return reflect(wI, nn);
+}
+
 __device__ __forceinline__ f2 mirrorLobe(f3 wI, f3 wO, f3 n, float cosTheta) {                             // :67-68, 83-84, 100-101
     bool isMirrorDirection = fabsf(dot(reflect(wI, n), wO) - 1.0f) < MRT_ANGLE_EPSILON;
     f2 r; r.x = isMirrorDirection ? cosTheta : 0.0f; r.y = 1.0f;
@@ -248,6 +312,9 @@ __device__ __forceinline__ void ray_generator(PathState& st, const float4* noise
 // the early-out of :122-126 is the caller's).  `noise` = tile of slot (frame + bounce)%3 (Renderer.mm:538).
 // Returns true iff the light-sampling ray is live (validLightTriangle, :164,173); `sh` is written only inside
 // the NEE branch, exactly like the buffer fields at :171-175.
+// EXT = true compiles the optics extension in (alias light selection, refraction, dispersion — chosen by S.extFlags);
+// the EXT = false instantiation is the reference's behaviour and the only one launched while S.extFlags == 0.
+template <bool EXT = false>
 __device__ __forceinline__ bool intersection_handler(const DeviceScene& S, const HitRec& hit, PathState& st, ShadowRay& sh,
                                                      bool& neeBranch, const float4* noise, uint32_t frameIndex,
                                                      uint32_t maxPathLength, uint32_t x, uint32_t y) {
@@ -263,7 +330,10 @@ __device__ __forceinline__ bool intersection_handler(const DeviceScene& S, const
     neeBranch = bounce + 1 < maxPathLength;
 
     if (neeBranch) {                                                                            // :150-176
-        Light sel = load_light(S, selectLightTriangle(noiseSample.z, S.lightCdf, S.lightCount, S.lightGuide, S.lightGuideBuckets));
+        uint32_t selected;
+        if (EXT && (S.extFlags & MRT_EXT_ALIAS_LIGHTS)) selected = selectLightAlias(noiseSample.z, S.lightAlias, S.lightCount);
+        else selected = selectLightTriangle(noiseSample.z, S.lightCdf, S.lightCount, S.lightGuide, S.lightGuideBuckets);
+        Light sel = load_light(S, selected);
         Vtx lightVertex = interpolate(sel.v1, sel.v2, sel.v3, barycentric(noiseSample.w, noiseSample.x));
         f3 directionToLight;
         float lightPdf = lightTriangleSamplePDF(sel.pdf, sel.area, hitVertex.v, lightVertex, directionToLight);
@@ -295,8 +365,16 @@ __device__ __forceinline__ bool intersection_handler(const DeviceScene& S, const
 
     {                                                                                           // :200-211
         float pdf = 0.0f, bsdf = 0.0f, ior = 0.0f;
-        st.direction = generateNextBounce(material, st.direction, st.ior, hitVertex.n, noiseSample, bsdf, pdf, ior);
-        st.origin = hitVertex.v + hitVertex.n * MRT_DISTANCE_EPSILON;
+        f3 side = hitVertex.n;
+        if (EXT && (S.extFlags & MRT_EXT_REFRACTION) && material.type == MRT_MATERIAL_SMOOTH_DIELECTRIC) {
+            f3 channelScale;
+            st.direction = refractiveBounce(material, S, st.direction, st.ior, st.throughput, hitVertex.n, noiseSample, bsdf, pdf, ior, channelScale);
+            st.throughput = mk3(st.throughput.x * channelScale.x, st.throughput.y * channelScale.y, st.throughput.z * channelScale.z);
+            if (dot(st.direction, hitVertex.n) < 0.0f) side = -hitVertex.n;      // continue (and sample lights) on the far side
+        } else {
+            st.direction = generateNextBounce(material, st.direction, st.ior, hitVertex.n, noiseSample, bsdf, pdf, ior);
+        }
+        st.origin = hitVertex.v + side * MRT_DISTANCE_EPSILON;
         st.pdf = pdf;
         st.prevDiffuse = float(material.type == MRT_MATERIAL_DIFFUSE);
         st.bounce = float(bounce + 1);

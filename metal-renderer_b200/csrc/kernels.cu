@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(256) k_intersect(DeviceScene S, const char* __
 }
 
 // ---- intersectionHandler (Shaders.metal:105-212) ----------------------------------------------------------
+template <bool EXT>
 __global__ void __launch_bounds__(256) k_shade(DeviceScene S, const mrt_intersection* __restrict__ isects, mrt_ray* __restrict__ rays,
                                                mrt_light_sampling_ray* __restrict__ lightRays, const float4* __restrict__ noise,
                                                uint32_t frameIndex, uint32_t maxPathLength, Grid2D g) {
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(256) k_shade(DeviceScene S, const mrt_intersec
     st.pdf = r4.x; st.prevDiffuse = r4.y; st.bounce = r4.z; st.ior = r4.w;
     HitRec hit; hit.t = is.x; hit.tri = __float_as_uint(is.y); hit.u = is.z; hit.v = is.w;
     ShadowRay sh; bool nee;
-    bool live = intersection_handler(S, hit, st, sh, nee, noise, frameIndex, maxPathLength, x, y);
+    bool live = intersection_handler<EXT>(S, hit, st, sh, nee, noise, frameIndex, maxPathLength, x, y);
     if (nee) {                                                                          // :171-175
         float4* l = reinterpret_cast<float4*>(lightRays + i);
         float lmin = lightRays[i].minDistance;
@@ -298,7 +299,8 @@ void launch_intersect(cudaStream_t s, const DeviceScene& S, const void* rays, ui
 void launch_shade(cudaStream_t s, const DeviceScene& S, const mrt_intersection* isects, mrt_ray* rays,
                   mrt_light_sampling_ray* lightRays, const float4* noiseTile, uint32_t frameIndex, uint32_t maxPathLength,
                   Grid2D g) {
-    k_shade<<<blocks_for(g.W * g.H), 256, 0, s>>>(S, isects, rays, lightRays, noiseTile, frameIndex, maxPathLength, g);
+    if (S.extFlags) k_shade<true><<<blocks_for(g.W * g.H), 256, 0, s>>>(S, isects, rays, lightRays, noiseTile, frameIndex, maxPathLength, g);
+    else k_shade<false><<<blocks_for(g.W * g.H), 256, 0, s>>>(S, isects, rays, lightRays, noiseTile, frameIndex, maxPathLength, g);
 }
 void launch_shadow_resolve(cudaStream_t s, const mrt_intersection* isects, mrt_ray* rays,
                            const mrt_light_sampling_ray* lightRays, Grid2D g) {

@@ -178,7 +178,7 @@ __device__ __forceinline__ uint32_t wf_sort_key(const WfBuffers& b, f3 o, f3 d) 
     return (b.sortMode & 1u) ? ((oct << (3u * b.sortBits)) | cell) : ((cell << 3) | oct);
 }
 
-template <bool COUNT, int MINB, bool SORT>
+template <bool COUNT, int MINB, bool SORT, bool EXT = false>
 __global__ void __launch_bounds__(256, MINB) k_wf_shade(RenderParams P, WfBuffers b, uint32_t outParity, uint32_t first, uint32_t seqHost) {
     __shared__ uint32_t sE[8], sS[8], sN[8], sW[8], sD[8], sBase[5];
     const uint32_t seq = seqHost + b.ctl[MRT_CTL_LAUNCHES];        // varies the probe sequence from wave to wave (graph replays included)
@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(256, MINB) k_wf_shade(RenderParams P, WfBuffer
                 const uint32_t s = (e.x + uint32_t(st.bounce)) % 3u;                   // Renderer.mm:538
                 const uint32_t t = s == 0 ? e.y : (s == 1 ? e.z : e.w);
                 ShadowRay sh; bool nee;
-                const bool live = intersection_handler(P.S, hit, st, sh, nee, P.noisePool + t * tileStride, e.x,
+                const bool live = intersection_handler<EXT>(P.S, hit, st, sh, nee, P.noisePool + t * tileStride, e.x,
                                                        P.maxPathLength, x, y);
                 if (live) {
                     liveShadow = 1;
@@ -539,6 +539,11 @@ void launch_wf_shade(cudaStream_t s, const RenderParams& p, const WfBuffers& b, 
     const uint32_t blocks = (b.slots + 255u) / 256u;
     const uint32_t outParity = first ? 0u : ((wave + 1u) & 1u);               // shade(w) fills the queues trace(w+1) consumes
     const uint32_t f = first ? 1u : 0u;
+    if (p.S.extFlags) {                                 // optics extension (mrt_set_extensions): its own instantiation, so the
+        if (countRays) k_wf_shade<true, 4, false, true><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave);     // default kernel's code is untouched
+        else           k_wf_shade<false, 4, false, true><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave);
+        return;
+    }
     // 4 blocks per SM = 64 registers with a 56-byte spill frame; 3 = 80 registers.  The kernel is latency-bound (ncu pass O:
     // 36 % warps active, long scoreboard), so occupancy wins: +3.6 % per step in pass P
 #define MRT_LAUNCH_SHADE_S(MB, SORT) do { if (countRays) k_wf_shade<true, MB, SORT><<<blocks, 256, 0, s>>>(p, b, outParity, f, wave); \

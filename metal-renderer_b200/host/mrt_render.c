@@ -21,6 +21,9 @@
  *                   [--tone] [--srgb]            presentation pass on the written image (Shaders.metal:43-51; one GPU)
  *                   [--resume file.ckpt]         continue an earlier render (frames then count from the stored index; one GPU)
  *                   [--checkpoint file.ckpt]     save image + frame index + noise slots after rendering (one GPU)
+ *                   [--optics refraction|dispersion|alias|all] [--spread D]
+ *                                                optics extension, NOT in the reference (mrt_set_extensions): Snell refraction,
+ *                                                per-channel index material.ior + D * (c - 1) (default D 0.02), alias-table lights
  */
 #define _POSIX_C_SOURCE 200809L
 #include <stdio.h>
@@ -50,7 +53,8 @@ static int write_pfm(const char* path, const float* rgba, unsigned w, unsigned h
 
 typedef struct options {
     const char* scene_name; const char* out; const char* resume; const char* checkpoint;
-    unsigned tone, srgb, w, h, frames, depth, pipeline, rows;
+    unsigned tone, srgb, w, h, frames, depth, pipeline, rows, optics;
+    float spread;
     int devices[16]; int n_devices;
     unsigned long long seed;
 } options;
@@ -86,6 +90,7 @@ static void* worker_main(void* arg) {
     cfg.accumulate_mode = o->rows ? MRT_ACCUM_MEAN : MRT_ACCUM_SUM;
     WCHECK(mrt_create(&cfg, &ctx));
     WCHECK(mrt_set_prepared_scene(ctx, w->prepared));
+    if (o->optics) WCHECK(mrt_set_extensions(ctx, o->optics, o->spread));
     WCHECK(mrt_resize(ctx, o->w, o->h));
     WCHECK(mrt_stream_handle(ctx, &stream));
     WCHECK(mrt_image_device_ptr(ctx, &image_dev, &image_bytes));
@@ -195,7 +200,7 @@ int main(int argc, char** argv) {
     options o;
     memset(&o, 0, sizeof o);
     o.scene_name = "cornell"; o.w = 256; o.h = 256; o.frames = 16; o.depth = MRT_MAX_PATH_LENGTH; o.pipeline = MRT_PIPELINE_AUTO;
-    o.seed = 1; o.n_devices = 1; o.devices[0] = 0;
+    o.seed = 1; o.n_devices = 1; o.devices[0] = 0; o.spread = 0.02f;
     unsigned first = 0;
     for (int i = 1; i < argc; ++i) {
         const char* a = argv[i];
@@ -221,6 +226,15 @@ int main(int argc, char** argv) {
         else if (!strcmp(a, "--out")) { o.out = v; ++i; }
         else if (!strcmp(a, "--resume")) { o.resume = v; ++i; }
         else if (!strcmp(a, "--checkpoint")) { o.checkpoint = v; ++i; }
+        else if (!strcmp(a, "--optics")) {
+            if (!strcmp(v, "refraction")) o.optics = MRT_EXT_REFRACTION;
+            else if (!strcmp(v, "dispersion")) o.optics = MRT_EXT_REFRACTION | MRT_EXT_DISPERSION;
+            else if (!strcmp(v, "alias")) o.optics = MRT_EXT_ALIAS_LIGHTS;
+            else if (!strcmp(v, "all")) o.optics = MRT_EXT_REFRACTION | MRT_EXT_DISPERSION | MRT_EXT_ALIAS_LIGHTS;
+            else { fprintf(stderr, "bad --optics\n"); return 2; }
+            ++i;
+        }
+        else if (!strcmp(a, "--spread")) { o.spread = (float)atof(v); ++i; }
         else if (!strcmp(a, "--tone")) o.tone = 1;
         else if (!strcmp(a, "--srgb")) o.srgb = 1;
         else { fprintf(stderr, "unknown argument %s\n", a); return 2; }
@@ -254,6 +268,7 @@ int main(int argc, char** argv) {
     mrt_ctx* ctx = NULL;
     CHECK(mrt_create(&cfg, &ctx));
     CHECK(mrt_set_scene_from(ctx, scene));
+    if (o.optics) CHECK(mrt_set_extensions(ctx, o.optics, o.spread));
     CHECK(mrt_resize(ctx, w, h));
 
     if (o.resume) {                                              /* restores size, image, frame index and noise slots */

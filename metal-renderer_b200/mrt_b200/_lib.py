@@ -35,6 +35,7 @@ PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_STAGED = range(
 ACCUM_MEAN, ACCUM_SUM, ACCUM_REPLACE = range(3)
 COMPARE_DISABLED, COMPARE_ABSOLUTE_VALUE, COMPARE_REF_TO_COLOR, COMPARE_COLOR_TO_REF, COMPARE_LUMINANCE = range(5)   # Raytracing.h:27-31
 SCHEDULE_GRAPH, SCHEDULE_HOST_LOOP = 0, 1   # mrt_set_wave_schedule
+EXT_REFRACTION, EXT_DISPERSION, EXT_ALIAS_LIGHTS = 1, 2, 4   # mrt_set_extensions (beyond the reference)
 NOALLOC_MAX_RAYS, NOALLOC_MAX_STRIDE = 65536, 80   # mrt_intersect_host_noalloc (include/mrt.h)
 PROFILE_TRACE_TIME, PROFILE_VISITS = 1, 2      # mrt_set_profile flags (include/mrt.h)
 BUF_RAYS, BUF_LIGHT_RAYS, BUF_INTERSECTIONS, BUF_IMAGE = range(4)
@@ -104,6 +105,8 @@ SIGNATURES = {
     "mrt_set_accumulate_mode": (C.c_int, [_P, _U32]),
     "mrt_set_pipeline": (C.c_int, [_P, _U32]),
     "mrt_set_wave_schedule": (C.c_int, [_P, _U32]),
+    "mrt_set_extensions": (C.c_int, [_P, _U32, C.c_float]),
+    "mrt_build_alias_table": (C.c_int, [_P, _U32, _P, _P]),
     "mrt_set_profile": (C.c_int, [_P, _U32]),
     "mrt_raygen": (C.c_int, [_P, _U32]),
     "mrt_intersect": (C.c_int, [_P, _U32]),

@@ -86,6 +86,11 @@ class Renderer:
         """SCHEDULE_GRAPH (default: one CUDA graph per batch, device-side stop) or SCHEDULE_HOST_LOOP."""
         L.check(L.lib().mrt_set_wave_schedule(self._ctx, schedule))
 
+    def set_extensions(self, flags, dispersion=0.0):
+        """Optics extension, beyond the reference (include/mrt.h): OR of EXT_REFRACTION, EXT_DISPERSION, EXT_ALIAS_LIGHTS;
+        0 restores the reference's behaviour."""
+        L.check(L.lib().mrt_set_extensions(self._ctx, int(flags), float(dispersion)))
+
     def set_pipeline(self, pipeline):
         L.check(L.lib().mrt_set_pipeline(self._ctx, pipeline))
 

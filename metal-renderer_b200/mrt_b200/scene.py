@@ -97,3 +97,12 @@ def bvh_selftest(name, seed=0, n_rays=2000, ray_seed=1):
     finally:
         L.lib().mrt_scene_destroy(handle)
     return {n: getattr(rep, n) for n, _ in L.BvhReport._fields_}
+
+
+def build_alias_table(pdf):
+    """(prob, alias) of the Walker/Vose table mrt_set_scene builds from the light pdfs (optics extension, host code)."""
+    pdf = np.ascontiguousarray(pdf, dtype=np.float32)
+    prob = np.zeros(len(pdf), dtype=np.float32)
+    alias = np.zeros(len(pdf), dtype=np.uint32)
+    L.check(L.lib().mrt_build_alias_table(L.ptr(pdf), len(pdf), L.ptr(prob), L.ptr(alias)))
+    return prob, alias

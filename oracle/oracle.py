@@ -71,6 +71,9 @@ def lib():
             "orc_lightTriangleSamplePDF": (F, [F, F, P, P, P]),
             "orc_triangle_test": (None, [P, P, F, F, P, P, P, P, P]), "orc_sizeof": (U, [U]),
             "orc_display": (None, [P, U, U, U, U, U, F, P, U, U, P]), "orc_toSRGB": (F, [F]),
+            "orc_set_extensions": (None, [P, U, F, P, P, U]),
+            "orc_refractiveBounce": (None, [P, U, F, P, F, P, P, P, P, P, P]),
+            "orc_selectLightAlias": (U, [F, P, P, U]),
         }
         for n, (r, a) in sig.items():
             fn = getattr(h, n)
@@ -114,6 +117,15 @@ class Oracle:
 
     def set_row_shard(self, first, stride):
         lib().orc_set_row_shard(self._c, first, stride)
+
+    def set_extensions(self, flags, dispersion=0.0, alias_prob=None, alias_index=None):
+        """Optics extension (beyond the reference, orc_shading.h).  The alias table comes from the caller."""
+        if alias_prob is None:
+            lib().orc_set_extensions(self._c, flags, dispersion, None, None, 0)
+        else:
+            prob = np.ascontiguousarray(alias_prob, dtype=np.float32)
+            idx = np.ascontiguousarray(alias_index, dtype=np.uint32)
+            lib().orc_set_extensions(self._c, flags, dispersion, _p(prob), _p(idx), len(prob))
 
     def init_raytracing(self, scene):
         self._scene = scene     # keep arrays alive during the call only; oracle copies them

@@ -43,6 +43,8 @@ struct orc_ctx {
     std::vector<float> noise[NOISE_SLOTS];
     std::atomic<uint64_t> primaryRays{0}, shadowRays{0}, nodesVisited{0}, trisTested{0};
     bool countVisits = false;
+    Extensions ext;                          // optics extension, off unless orc_set_extensions is called
+    std::vector<float> aliasProb; std::vector<uint32_t> aliasIndex;
 };
 
 static void intersect_range(orc_ctx* c, const char* rayBase, size_t stride, Intersection* out, size_t begin, size_t end,
@@ -93,7 +95,7 @@ static void frame_range(orc_ctx* c, uint32_t frame, const float* const slotTiles
         each([&](size_t, uint32_t x, uint32_t y) {
             intersectionHandler(c->intersections.data(), c->vertices.data(), c->references.data(), c->materials.data(), sd,
                                 c->lights.data(), c->rays.data(), slotTiles[(frame + i) % 3], c->lightRays.data(),
-                                c->maxPathLength, x, y, W); });
+                                c->maxPathLength, x, y, W, c->ext); });
         each([&](size_t k, uint32_t, uint32_t) {
             intersect_range(c, (const char*)c->lightRays.data(), sizeof(LightSamplingRay), c->intersections.data(), k, k + 1, &liveShadow, pnv, ptt, c->useBvh); });
         each([&](size_t k, uint32_t, uint32_t) { lightSamplingHandler(c->intersections.data(), c->rays.data(), c->lightRays.data(), (uint32_t)k); });
@@ -117,6 +119,22 @@ void orc_set_options(orc_ctx* c, uint32_t useBvh, uint32_t countVisits, uint32_t
     c->useBvh = useBvh != 0; c->countVisits = countVisits != 0; c->animateNoise = animateNoise;
 }
 void orc_set_accumulate_mode(orc_ctx* c, uint32_t mode) { c->accumMode = mode; }
+// optics extension (beyond the reference; orc_shading.h).  The alias table is an input, like the light cdf is.
+void orc_set_extensions(orc_ctx* c, uint32_t flags, float dispersion, const float* aliasProb, const uint32_t* aliasIndex, uint32_t n) {
+    c->aliasProb.clear(); c->aliasIndex.clear();
+    if (aliasProb && aliasIndex) { c->aliasProb.assign(aliasProb, aliasProb + n); c->aliasIndex.assign(aliasIndex, aliasIndex + n); }
+    c->ext.flags = flags; c->ext.dispersion = (flags & EXT_DISPERSION) ? dispersion : 0.0f;
+    c->ext.aliasProb = c->aliasProb.data(); c->ext.aliasIndex = c->aliasIndex.data();
+}
+void orc_refractiveBounce(const Material* m, uint32_t flags, float dispersion, const float* dir, float rayIor, const float* throughput3,
+                          const float* n, const float* noise4, float* out3, float* bsdfPdfIor3, float* channelScale3) {
+    Extensions e; e.flags = flags; e.dispersion = dispersion;
+    Spectrum t; for (int i = 0; i < 3; ++i) t.values[i] = throughput3[i];
+    float bsdf = 0, pdf = 0, ior = 0;
+    st3(out3, refractiveBounce(*m, e, ld3(dir), rayIor, t, ld3(n), f4{noise4[0], noise4[1], noise4[2], noise4[3]}, bsdf, pdf, ior, channelScale3));
+    bsdfPdfIor3[0] = bsdf; bsdfPdfIor3[1] = pdf; bsdfPdfIor3[2] = ior;
+}
+uint32_t orc_selectLightAlias(float xi, const float* prob, const uint32_t* alias, uint32_t n) { return selectLightAlias(xi, prob, alias, n); }
 void orc_set_row_shard(orc_ctx* c, uint32_t first, uint32_t stride) { c->rowFirst = first; c->rowStride = stride ? stride : 1; }
 
 // buffer upload + acceleration structure of initRaytracing (Renderer.mm:450-469)
@@ -165,7 +183,7 @@ void orc_shade(orc_ctx* c, uint32_t frame, uint32_t bounceIteration) {
         for (size_t i = b; i < e; ++i) { uint32_t y = (uint32_t)(i / c->W), x = (uint32_t)(i % c->W);
             if (owns_row(c, y)) intersectionHandler(c->intersections.data(), c->vertices.data(), c->references.data(),
                 c->materials.data(), sd, c->lights.data(), c->rays.data(), c->noise[(frame + bounceIteration) % 3].data(),
-                c->lightRays.data(), c->maxPathLength, x, y, c->W); } });
+                c->lightRays.data(), c->maxPathLength, x, y, c->W, c->ext); } });
 }
 void orc_shadow_resolve(orc_ctx* c) {
     parallel_chunks(c->threads, (size_t)c->W * c->H, 8192, [&](size_t b, size_t e) {

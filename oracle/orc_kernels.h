@@ -39,7 +39,8 @@ static inline void intersectionHandler(const Intersection* intersections, const 
                                        const TriangleReference* referenceBuffer, const Material* materialBuffer,
                                        const SharedData& sharedData, const LightTriangle* lightTriangles,
                                        Ray* primaryRays, const float* noise, LightSamplingRay* lightSamplingRays,
-                                       uint32_t maxPathLength, uint32_t x, uint32_t y, uint32_t W) {
+                                       uint32_t maxPathLength, uint32_t x, uint32_t y, uint32_t W,
+                                       const Extensions& ext = Extensions()) {            // default = the reference
     uint32_t rayIndex = y * W + x;
     lightSamplingRays[rayIndex].maxDistance = -1.0f;                                       // :119
     const Intersection& intersection = intersections[rayIndex];
@@ -63,8 +64,9 @@ static inline void intersectionHandler(const Intersection* intersections, const 
 
     // light sampling (:150-176)
     if (bounce + 1 < maxPathLength) {
-        const LightTriangle& selected = selectLightTriangle(noiseSample.z, lightTriangles,
-                                                            (int)sharedData.lightTrianglesCount);
+        const LightTriangle& selected = (ext.flags & EXT_ALIAS_LIGHTS)
+            ? lightTriangles[selectLightAlias(noiseSample.z, ext.aliasProb, ext.aliasIndex, sharedData.lightTrianglesCount)]
+            : selectLightTriangle(noiseSample.z, lightTriangles, (int)sharedData.lightTrianglesCount);
         Vtx lightVertex = interpolate(load_vertex(selected.v1), load_vertex(selected.v2), load_vertex(selected.v3),
                                       barycentric(f2{noiseSample.w, noiseSample.x}));     // noiseSample.wx (:154)
         f3 directionToLight;
@@ -107,9 +109,20 @@ static inline void intersectionHandler(const Intersection* intersections, const 
     // next bounce (:200-211)
     {
         float pdf = 0.0f, bsdf = 0.0f, ior = 0.0f;
-        f3 dir = generateNextBounce(material, ld3(ray.direction), ray.params[3], hitVertex.n, noiseSample, bsdf, pdf, ior);
+        f3 dir, side = hitVertex.n;
+        if ((ext.flags & EXT_REFRACTION) && material.materialType == MATERIAL_SMOOTH_DIELECTRIC) {    // extension, see orc_shading.h
+            float channelScale[3];
+            dir = refractiveBounce(material, ext, ld3(ray.direction), ray.params[3], ray.throughput, hitVertex.n, noiseSample,
+                                   bsdf, pdf, ior, channelScale);
+            for (int i = 0; i < 3; ++i) ray.throughput.values[i] *= channelScale[i];
+            if (dot(dir, hitVertex.n) < 0.0f) side = -hitVertex.n;
+            // the light-sampling ray of this hit starts where the path continues from (far side after a transmission)
+            if (bounce + 1 < maxPathLength) st3(lightSamplingRays[rayIndex].origin, hitVertex.v + side * DISTANCE_EPSILON);
+        } else {
+            dir = generateNextBounce(material, ld3(ray.direction), ray.params[3], hitVertex.n, noiseSample, bsdf, pdf, ior);
+        }
         st3(ray.direction, dir);
-        st3(ray.origin, hitVertex.v + hitVertex.n * DISTANCE_EPSILON);
+        st3(ray.origin, hitVertex.v + side * DISTANCE_EPSILON);
         ray.maxDistance = INFINITY;
         ray.params[0] = pdf;
         ray.params[1] = float(material.materialType == MATERIAL_DIFFUSE);

@@ -186,6 +186,63 @@ static inline f3 generateNextBounce(const Material& material, f3 rayDirection, f
     return wO;
 }
 
+// ---- optics extension: BEYOND THE REFERENCE — PARITY UNPINNED BY CONSTRUCTION -------------------
+// Nothing below restates reference code: the reference keeps wO = wI at dielectrics (:157) and scans the CDF (:49-54).
+// This is the checker's own statement of the extension include/mrt.h documents under mrt_set_extensions; what it is
+// checked against are closed forms (tests/test_optics_extension.py), not the reference.
+struct Extensions {
+    uint32_t flags = 0;             // EXT_* bits
+    float dispersion = 0.0f;
+    const float* aliasProb = nullptr;       // alias table handed in by the test (built by the product's host code and
+    const uint32_t* aliasIndex = nullptr;   // verified against the pdfs separately)
+};
+enum { EXT_REFRACTION = 1, EXT_DISPERSION = 2, EXT_ALIAS_LIGHTS = 4 };
+static const float AIR_IOR = 1.00029f;      // the generator's Ray.params.w (Shaders.metal:99)
+
+static inline uint32_t selectLightAlias(float xi, const float* prob, const uint32_t* alias, uint32_t trianglesCount) {
+    if (trianglesCount == 0) return 0;
+    float s = std::fmin(std::fmax(xi, 0.0f), 1.0f) * float(trianglesCount);
+    uint32_t slot = std::min(uint32_t(s), trianglesCount - 1u);
+    return (s - float(slot)) < prob[slot] ? slot : alias[slot];
+}
+
+// Snell refraction / total internal reflection / one-channel dispersion at a smooth dielectric.
+static inline f3 refractiveBounce(const Material& material, const Extensions& ext, f3 wI, float rayIor, const Spectrum& throughput,
+                                  f3 n, f4 noiseSample, float& bsdf, float& pdf, float& ior, float channelScale[3]) {
+    float cosN = dot(n, -wI);
+    bool entering = cosN > 0.0f;
+    f3 nn = entering ? n : -n;
+    float etaI = rayIor;
+    float etaT = entering ? material.ior : AIR_IOR;
+    float fI = fresnel(nn, -wI, etaI, etaT);
+    channelScale[0] = channelScale[1] = channelScale[2] = 1.0f;
+    ior = rayIor;
+    if (fI < noiseSample.y) {
+        if (entering && (ext.flags & EXT_DISPERSION) && ext.dispersion != 0.0f) {
+            uint32_t k = 0;
+            for (int i = 0; i < 3; ++i) k += throughput.values[i] != 0.0f;
+            if (k > 0) {
+                uint32_t rank = std::min(uint32_t(noiseSample.x * float(k)), k - 1u), seen = 0, c = 3;
+                for (uint32_t i = 0; i < 3; ++i)
+                    if (throughput.values[i] != 0.0f) { if (seen == rank && c == 3) c = i; ++seen; }
+                for (uint32_t i = 0; i < 3; ++i) channelScale[i] = i == c ? float(k) : 0.0f;
+                etaT = material.ior + ext.dispersion * (float(c) - 1.0f);
+            }
+        }
+        float eta = etaI / etaT;
+        float cosI = clampf(dot(nn, -wI), 0.0f, 1.0f);
+        float sin2T = (eta * eta) * (1.0f - cosI * cosI);
+        if (sin2T < 1.0f) {
+            float cosT = std::sqrt(1.0f - sin2T);
+            ior = etaT; bsdf = eta * eta; pdf = 1.0f;
+            return normalize(wI * eta + nn * (eta * cosI - cosT));
+        }
+        channelScale[0] = channelScale[1] = channelScale[2] = 1.0f;
+    }
+    bsdf = 1.0f; pdf = 1.0f;
+    return reflect(wI, nn);
+}
+
 // :181-190 — solid-angle pdf of a point on a light triangle, with validity mask; outputs unit direction
 static inline float lightTriangleSamplePDF(float trianglePdf, float triangleArea, f3 source, const Vtx& sample,
                                            f3& directionToLight) {
