@@ -4,7 +4,8 @@
 // closed source, so triangulation and vertex order are UNPINNED; this loader documents its own choices:
 //   * a Vertex is a unique (position index, normal index) pair, in order of first use; texcoords are dropped
 //     (Renderer.mm:365-369 drops them too);
-//   * polygons are fan-triangulated (v0, v[i], v[i+1]); the water scenes' 7,088 quads become 14,176 triangles;
+//   * polygons are fan-triangulated (v0, v[i], v[i+1]) (the reference's water scenes need none: their 7,088 faces are
+//     triangles already);
 //   * faces without normals get the geometric face normal;
 //   * triangles are emitted grouped by material in order of first `usemtl` (SceneKit makes one geometry element
 //     per material, Renderer.mm:375-377), so triangle IDs are defined by THIS loader for oracle and GPU alike;
