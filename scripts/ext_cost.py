@@ -19,6 +19,8 @@ R, D, A = m.EXT_REFRACTION, m.EXT_DISPERSION, m.EXT_ALIAS_LIGHTS
 for label, flags, disp in (("off", 0, 0.0), ("refraction", R, 0.0), ("dispersion", R | D, 0.02), ("alias", A, 0.0), ("all", R | D | A, 0.02), ("off again", 0, 0.0)):
     r.set_extensions(flags, disp)
     r.drawable_size_will_change(w, h)
+    for slot in range(3):
+        r.update_noise(slot, m.noise_tile(seed, 0xFFFFFFFF))
     for _ in range(2):
         r.draw(n, tiles, first_frame=0, sync=False)
     r.sync(); r.reset_stats()
