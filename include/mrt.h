@@ -184,7 +184,8 @@ int mrt_set_wave_schedule(mrt_ctx* ctx, uint32_t schedule);
  *                        than 3 would change every ABI struct that embeds a Spectrum and is NOT built.
  *   MRT_EXT_ALIAS_LIGHTS light triangles are selected through a Walker/Vose alias table of the same pdfs (2 loads)
  *                        instead of the CDF search of KernelHelpers.h:49-54; same expectation, different samples.
- * Wavefront and staged pipelines; MRT_E_STATE under MRT_PIPELINE_MEGAKERNEL. */
+ * Wavefront and staged pipelines; MRT_E_STATE under MRT_PIPELINE_MEGAKERNEL.  The setting belongs to the ctx, survives
+ * mrt_set_scene / mrt_resize and is NOT stored by mrt_checkpoint_save: set it again after mrt_checkpoint_load. */
 enum { MRT_EXT_REFRACTION = 1, MRT_EXT_DISPERSION = 2, MRT_EXT_ALIAS_LIGHTS = 4 };
 int mrt_set_extensions(mrt_ctx* ctx, uint32_t flags, float dispersion);
 /* The alias table mrt_set_scene builds from the light pdfs (host code, no GPU): slot i keeps itself when the fraction

@@ -288,3 +288,19 @@ def test_dispersion_does_not_change_the_mean_image():
     assert ok.mean() > 0.99 and a[ok].min() >= 0.0 and b[ok].min() >= 0.0
     # channel selection is unbiased: the image mean moves by noise only
     assert np.allclose(a[ok].mean(axis=0), b[ok].mean(axis=0), rtol=0.05), (a[ok].mean(axis=0), b[ok].mean(axis=0))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,seed", [("spheres-1m", 3), ("many-lights", 5)])
+def test_extension_bit_exact_at_baseline_size(name, seed):
+    """BASELINE configs 3 and 5 (the two with smooth dielectrics) at 1080p, depth 8, every extension on: 2 frames of the
+    production pipeline against the restatement on all host cores."""
+    scene = m.Scene.procedural(name, seed)
+    r, o = setup_pair(scene, 1920, 1080, seed=seed, max_path_length=8, renderer_kwargs=dict(pipeline=m.PIPELINE_WAVEFRONT))
+    enable(r, o, scene, ALL, 0.02)
+    tiles = m.noise_tiles(seed, 0, 2)
+    r.draw(2, tiles); o.draw(2, tiles)
+    gi, oi = r.save_current_image(), o.save_current_image()
+    assert bits_equal(gi, oi), f"image differs on {np.mean(gi.view(np.uint32) != oi.view(np.uint32)):.3%} of the words"
+    st, oc = r.stats(), o.counts()
+    assert (st["primary_rays"], st["shadow_rays"]) == (oc["primary_rays"], oc["shadow_rays"])
