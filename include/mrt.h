@@ -182,11 +182,14 @@ int mrt_set_wave_schedule(mrt_ctx* ctx, uint32_t schedule);
  *                        dispersion * (c - 1); a path entering a medium keeps ONE live channel (uniform choice, weight =
  *                        number of live channels).  The 3 channels are Spectrum.h:3's SPECTRUM_SAMPLES; more samples
  *                        than 3 would change every ABI struct that embeds a Spectrum and is NOT built.
+ *   MRT_EXT_CONTINUOUS_SPECTRUM (needs DISPERSION) the index is taken uniformly inside the kept channel's band,
+ *                        material.ior + dispersion * (c - 1 + u - 0.5), u uniform: refraction sampled at a continuum of
+ *                        wavelengths (no three separate ghost images) while radiometry stays 3 samples wide.
  *   MRT_EXT_ALIAS_LIGHTS light triangles are selected through a Walker/Vose alias table of the same pdfs (2 loads)
  *                        instead of the CDF search of KernelHelpers.h:49-54; same expectation, different samples.
  * Wavefront and staged pipelines; MRT_E_STATE under MRT_PIPELINE_MEGAKERNEL.  The setting belongs to the ctx, survives
  * mrt_set_scene / mrt_resize and is NOT stored by mrt_checkpoint_save: set it again after mrt_checkpoint_load. */
-enum { MRT_EXT_REFRACTION = 1, MRT_EXT_DISPERSION = 2, MRT_EXT_ALIAS_LIGHTS = 4 };
+enum { MRT_EXT_REFRACTION = 1, MRT_EXT_DISPERSION = 2, MRT_EXT_ALIAS_LIGHTS = 4, MRT_EXT_CONTINUOUS_SPECTRUM = 8 };
 int mrt_set_extensions(mrt_ctx* ctx, uint32_t flags, float dispersion);
 /* The alias table mrt_set_scene builds from the light pdfs (host code, no GPU): slot i keeps itself when the fraction
  * is below prob[i], else yields alias[i]. */

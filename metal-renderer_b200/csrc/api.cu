@@ -542,8 +542,10 @@ int mrt_set_wave_schedule(mrt_ctx* c, uint32_t schedule) {
 }
 int mrt_set_extensions(mrt_ctx* c, uint32_t flags, float dispersion) {
     NEED(c, MRT_E_INVALID, "ctx is NULL");
-    NEED((flags & ~(uint32_t)(MRT_EXT_REFRACTION | MRT_EXT_DISPERSION | MRT_EXT_ALIAS_LIGHTS)) == 0, MRT_E_INVALID, "unknown extension bit in 0x%x", flags);
+    NEED((flags & ~(uint32_t)(MRT_EXT_REFRACTION | MRT_EXT_DISPERSION | MRT_EXT_ALIAS_LIGHTS | MRT_EXT_CONTINUOUS_SPECTRUM)) == 0, MRT_E_INVALID,
+         "unknown extension bit in 0x%x", flags);
     NEED(!(flags & MRT_EXT_DISPERSION) || (flags & MRT_EXT_REFRACTION), MRT_E_INVALID, "MRT_EXT_DISPERSION needs MRT_EXT_REFRACTION");
+    NEED(!(flags & MRT_EXT_CONTINUOUS_SPECTRUM) || (flags & MRT_EXT_DISPERSION), MRT_E_INVALID, "MRT_EXT_CONTINUOUS_SPECTRUM needs MRT_EXT_DISPERSION");
     NEED(std::isfinite(dispersion) && std::fabs(dispersion) <= 0.5f, MRT_E_INVALID, "dispersion %g outside [-0.5, 0.5]", (double)dispersion);
     c->S.extFlags = flags; c->S.dispersion = (flags & MRT_EXT_DISPERSION) ? dispersion : 0.0f;
     return MRT_OK;

@@ -173,7 +173,10 @@ __device__ __forceinline__ uint32_t selectLightAlias(float xi, const float2* tab
 // delta lobes with bsdf/pdf = 1 and the transmitted radiance is scaled by (etaI/etaT)^2 (radiance transport from the
 // camera).  No stack of nested media.  Dispersion: a transmitted path entering the medium keeps ONE of its live
 // throughput channels (chosen uniformly with noise.x, weight = number of live channels) and refracts with that channel's
-// index; it carries that index until it leaves.  `channelScale` multiplies the throughput.
+// index; it carries that index until it leaves.  `channelScale` multiplies the throughput.  With
+// MRT_EXT_CONTINUOUS_SPECTRUM the index is taken at a uniformly random place inside the chosen band (noise.w, unused at a
+// dielectric otherwise) instead of at its centre: the refraction angle is sampled over a continuum of wavelengths
+// although the radiometry stays 3 samples wide.
 #define MRT_AIR_IOR 1.00029f
 __device__ __forceinline__ f3 refractiveBounce(const Mat& material, const DeviceScene& S, f3 wI, float rayIor, f3 throughput, f3 n,
                                                float4 noiseSample, float& bsdf, float& pdf, float& ior, f3& channelScale) {
@@ -197,7 +200,9 @@ __device__ __forceinline__ f3 refractiveBounce(const Mat& material, const Device
                 if (a2) { if (seen == rank && c == 3u) c = 2u; ++seen; }
                 const float w = float(k);
                 channelScale = mk3(c == 0u ? w : 0.0f, c == 1u ? w : 0.0f, c == 2u ? w : 0.0f);
-                etaT = material.ior + S.dispersion * (float(c) - 1.0f);
+                float band = float(c) - 1.0f;                               // -1, 0, +1: the centre of band c
+                if (S.extFlags & MRT_EXT_CONTINUOUS_SPECTRUM) band += noiseSample.w - 0.5f;   // anywhere inside the band
+                etaT = material.ior + S.dispersion * band;
             }
         }
         const float eta = __fdiv_rn(etaI, etaT);

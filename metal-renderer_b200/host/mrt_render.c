@@ -21,7 +21,7 @@
  *                   [--tone] [--srgb]            presentation pass on the written image (Shaders.metal:43-51; one GPU)
  *                   [--resume file.ckpt]         continue an earlier render (frames then count from the stored index; one GPU)
  *                   [--checkpoint file.ckpt]     save image + frame index + noise slots after rendering (one GPU)
- *                   [--optics refraction|dispersion|alias|all] [--spread D]
+ *                   [--optics refraction|dispersion|spectrum|alias|all] [--spread D]
  *                                                optics extension, NOT in the reference (mrt_set_extensions): Snell refraction,
  *                                                per-channel index material.ior + D * (c - 1) (default D 0.02), alias-table lights
  */
@@ -230,7 +230,8 @@ int main(int argc, char** argv) {
             if (!strcmp(v, "refraction")) o.optics = MRT_EXT_REFRACTION;
             else if (!strcmp(v, "dispersion")) o.optics = MRT_EXT_REFRACTION | MRT_EXT_DISPERSION;
             else if (!strcmp(v, "alias")) o.optics = MRT_EXT_ALIAS_LIGHTS;
-            else if (!strcmp(v, "all")) o.optics = MRT_EXT_REFRACTION | MRT_EXT_DISPERSION | MRT_EXT_ALIAS_LIGHTS;
+            else if (!strcmp(v, "spectrum")) o.optics = MRT_EXT_REFRACTION | MRT_EXT_DISPERSION | MRT_EXT_CONTINUOUS_SPECTRUM;
+            else if (!strcmp(v, "all")) o.optics = MRT_EXT_REFRACTION | MRT_EXT_DISPERSION | MRT_EXT_ALIAS_LIGHTS | MRT_EXT_CONTINUOUS_SPECTRUM;
             else { fprintf(stderr, "bad --optics\n"); return 2; }
             ++i;
         }

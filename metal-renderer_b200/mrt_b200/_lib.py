@@ -35,7 +35,7 @@ PIPELINE_AUTO, PIPELINE_MEGAKERNEL, PIPELINE_WAVEFRONT, PIPELINE_STAGED = range(
 ACCUM_MEAN, ACCUM_SUM, ACCUM_REPLACE = range(3)
 COMPARE_DISABLED, COMPARE_ABSOLUTE_VALUE, COMPARE_REF_TO_COLOR, COMPARE_COLOR_TO_REF, COMPARE_LUMINANCE = range(5)   # Raytracing.h:27-31
 SCHEDULE_GRAPH, SCHEDULE_HOST_LOOP = 0, 1   # mrt_set_wave_schedule
-EXT_REFRACTION, EXT_DISPERSION, EXT_ALIAS_LIGHTS = 1, 2, 4   # mrt_set_extensions (beyond the reference)
+EXT_REFRACTION, EXT_DISPERSION, EXT_ALIAS_LIGHTS, EXT_CONTINUOUS_SPECTRUM = 1, 2, 4, 8   # mrt_set_extensions (beyond the reference)
 NOALLOC_MAX_RAYS, NOALLOC_MAX_STRIDE = 65536, 80   # mrt_intersect_host_noalloc (include/mrt.h)
 PROFILE_TRACE_TIME, PROFILE_VISITS = 1, 2      # mrt_set_profile flags (include/mrt.h)
 BUF_RAYS, BUF_LIGHT_RAYS, BUF_INTERSECTIONS, BUF_IMAGE = range(4)

@@ -196,7 +196,7 @@ struct Extensions {
     const float* aliasProb = nullptr;       // alias table handed in by the test (built by the product's host code and
     const uint32_t* aliasIndex = nullptr;   // verified against the pdfs separately)
 };
-enum { EXT_REFRACTION = 1, EXT_DISPERSION = 2, EXT_ALIAS_LIGHTS = 4 };
+enum { EXT_REFRACTION = 1, EXT_DISPERSION = 2, EXT_ALIAS_LIGHTS = 4, EXT_CONTINUOUS_SPECTRUM = 8 };
 static const float AIR_IOR = 1.00029f;      // the generator's Ray.params.w (Shaders.metal:99)
 
 static inline uint32_t selectLightAlias(float xi, const float* prob, const uint32_t* alias, uint32_t trianglesCount) {
@@ -226,7 +226,9 @@ static inline f3 refractiveBounce(const Material& material, const Extensions& ex
                 for (uint32_t i = 0; i < 3; ++i)
                     if (throughput.values[i] != 0.0f) { if (seen == rank && c == 3) c = i; ++seen; }
                 for (uint32_t i = 0; i < 3; ++i) channelScale[i] = i == c ? float(k) : 0.0f;
-                etaT = material.ior + ext.dispersion * (float(c) - 1.0f);
+                float band = float(c) - 1.0f;
+                if (ext.flags & EXT_CONTINUOUS_SPECTRUM) band += noiseSample.w - 0.5f;
+                etaT = material.ior + ext.dispersion * band;
             }
         }
         float eta = etaI / etaT;

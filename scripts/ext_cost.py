@@ -15,8 +15,8 @@ r = m.Renderer(max_path_length=8)
 r.init_raytracing(scene)
 tiles = m.noise_tiles(seed, 0, n)
 out = {"scene": scene_name, "size": [w, h], "frames": n}
-R, D, A = m.EXT_REFRACTION, m.EXT_DISPERSION, m.EXT_ALIAS_LIGHTS
-for label, flags, disp in (("off", 0, 0.0), ("refraction", R, 0.0), ("dispersion", R | D, 0.02), ("alias", A, 0.0), ("all", R | D | A, 0.02), ("off again", 0, 0.0)):
+R, D, A, C = m.EXT_REFRACTION, m.EXT_DISPERSION, m.EXT_ALIAS_LIGHTS, m.EXT_CONTINUOUS_SPECTRUM
+for label, flags, disp in (("off", 0, 0.0), ("refraction", R, 0.0), ("dispersion", R | D, 0.02), ("alias", A, 0.0), ("spectrum", R | D | C, 0.02), ("all", R | D | A | C, 0.02), ("off again", 0, 0.0)):
     r.set_extensions(flags, disp)
     r.drawable_size_will_change(w, h)
     for slot in range(3):

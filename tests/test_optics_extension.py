@@ -87,6 +87,12 @@ def test_dispersion_keeps_one_channel_and_bends_blue_more():
     d, bpi, scale = refract(1.5, (0.3, 0.95393920141, 0.0), n, (0.1, 0.999, 0, 0), ray_ior=1.52, flags=flags, dispersion=0.02,
                             throughput=(0.0, 0.0, 1.0))
     assert list(scale) == [1.0, 1.0, 1.0] and bpi[2] == AIR and d[0] == pytest.approx(0.3 * 1.52 / float(AIR), abs=3e-6)
+    # continuous spectrum: the index moves inside the band with noise.w; the band centre (w = 0.5) is the discrete value
+    cont = flags | m.EXT_CONTINUOUS_SPECTRUM
+    for w, off in ((0.5, 0.0), (0.0, -0.5), (0.75, 0.25)):
+        _, bpi, scale = refract(1.5, wI, n, (0.9, 0.999, 0, w), flags=cont, dispersion=0.02)      # noise.x = 0.9: blue band
+        assert list(scale) == [0.0, 0.0, 3.0]
+        assert bpi[2] == np.float32(np.float32(1.5) + np.float32(0.02) * np.float32(np.float32(1.0) + (np.float32(w) - np.float32(0.5))))
     # without the DISPERSION bit the coefficient is ignored
     _, bpi, scale = refract(1.5, wI, n, (0.1, 0.999, 0, 0), flags=m.EXT_REFRACTION, dispersion=0.02)
     assert list(scale) == [1.0, 1.0, 1.0] and bpi[2] == np.float32(1.5)
@@ -158,8 +164,9 @@ def test_oracle_with_no_flags_is_the_reference_path():
 # ---- CUDA path against the restatement ---------------------------------------------------------------------------
 from helpers import bits_equal, mismatch_report, setup_pair  # noqa: E402
 
-ALL = m.EXT_REFRACTION | m.EXT_DISPERSION | m.EXT_ALIAS_LIGHTS
+ALL = m.EXT_REFRACTION | m.EXT_DISPERSION | m.EXT_ALIAS_LIGHTS | m.EXT_CONTINUOUS_SPECTRUM
 COMBOS = [pytest.param(m.EXT_REFRACTION, 0.0, id="refraction"), pytest.param(m.EXT_REFRACTION | m.EXT_DISPERSION, 0.03, id="dispersion"),
+          pytest.param(m.EXT_REFRACTION | m.EXT_DISPERSION | m.EXT_CONTINUOUS_SPECTRUM, 0.03, id="spectrum"),
           pytest.param(m.EXT_ALIAS_LIGHTS, 0.0, id="alias"), pytest.param(ALL, 0.02, id="all")]
 
 
@@ -231,7 +238,9 @@ def test_flags_zero_restores_the_reference_bits_and_bad_flags_are_rejected():
     r.draw(frames, tiles)
     assert_bits(r.save_current_image(), want, "after set_extensions(0)")
     with pytest.raises(m.MrtError, match="unknown extension bit"):
-        r.set_extensions(8)
+        r.set_extensions(16)
+    with pytest.raises(m.MrtError, match="needs MRT_EXT_DISPERSION"):
+        r.set_extensions(m.EXT_REFRACTION | m.EXT_CONTINUOUS_SPECTRUM)
     with pytest.raises(m.MrtError, match="needs MRT_EXT_REFRACTION"):
         r.set_extensions(m.EXT_DISPERSION, 0.01)
     with pytest.raises(m.MrtError, match="dispersion"):
