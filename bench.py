@@ -238,7 +238,7 @@ def parity_step(args, wl, m, D, scene, r, ep, coll, rank, world):
     r.raygen(0); r.intersect(m.BUF_RAYS)
     hits = r.read_buffer(m.BUF_INTERSECTIONS)["triangleIndex"].copy() if rank == 0 else None
     frames = k * world
-    sr = D.ShardedRenderer(ep, rank, world, coll, mode="samples")        # fresh accumulation state (world 1: running mean)
+    sr = D.ShardedRenderer(ep, rank, world, coll, mode="samples", reduce=args.reduce)   # fresh accumulation state (world 1: running mean)
     plan = D.plan_sample_shard(0, k, rank, world)
     tiles = m.noise_tiles(seed, plan.first_frame, plan.span)
     lead = {f: m.noise_tile(seed, f) for f in D.lead_in_frames(plan.first_frame)}
@@ -314,11 +314,11 @@ def run_ours(args, wl):
     torch.cuda.synchronize()
     tile_bytes = m.NOISE_TILE_FLOATS * 4
 
-    def make_stepper(frames_per_rank):
+    def make_stepper(frames_per_rank, reduce=None):
         """One step = ShardedRenderer.step (mrt_b200/distributed.py — the code the sharding tests run): `frames_per_rank`
         frames on every rank, one NCCL all-reduce of the sum image, normalisation.  Tiles are addressed inside the
         resident (device) or pinned (host) tile array: tile j = frame (step start + j) modulo the array."""
-        sr = D.ShardedRenderer(ep, rank, world, coll, mode="samples")
+        sr = D.ShardedRenderer(ep, rank, world, coll, mode="samples", reduce=reduce or args.reduce)
         n = frames_per_rank * world
 
         def step(tiles_ptr, readback):
@@ -432,6 +432,31 @@ def run_ours(args, wl):
                           "the device time of a step incl. the all-reduce, max over ranks; allreduce_ms is the event-timed collective "
                           "incl. the wait for the slowest rank; tail_waves = waves with fewer extension rays than half the path slots"}
 
+        # the same fixed-work step with the other reduction (csrc/peer.cu: one kernel per GPU over NVLink peer memory, no
+        # NCCL on the data path), so that both are on record whichever one --reduce selected
+        other = "peer" if args.reduce == "nccl" else "nccl"
+        try:
+            sr_o, step_o = make_stepper(fs, reduce=other)
+            sr_o.time_events = (2, 3)
+            for _ in range(3):
+                step_o(dev_tiles.data_ptr(), False)
+            barrier()
+            o_ms = []
+            r.event_record(4)
+            for _ in range(args.steps):
+                step_o(dev_tiles.data_ptr(), False)
+                r.sync()
+                o_ms.append(r.event_elapsed_ms(2, 3))
+            r.event_record(5)
+            barrier()
+            if other == "peer":
+                r.peer_status()
+            strong["other_reduce"] = {"reduce": other, "ms_total": reduce_ranks(r.event_elapsed_ms(4, 5)) / args.steps,
+                                      "reduce_ms": reduce_ranks(float(np.median(o_ms)))}
+        except Exception as e:                          # noqa: BLE001 — e.g. no CUDA IPC between the ranks' processes
+            strong["other_reduce"] = {"reduce": other, "unavailable": str(e)[:300]}
+        strong["reduce"] = args.reduce
+
     parity = None if args.no_parity else parity_step(args, wl, m, D, scene, r, ep, coll, rank, world)
 
     if rank == 0:
@@ -533,6 +558,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the untimed parity step against the oracle")
     ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the fixed-work (strong scaling) measurement")
+    ap.add_argument("--reduce", default="nccl", choices=["nccl", "peer"],
+                    help="N > 1: framebuffer reduction = copy + NCCL all-reduce + scale, or mrt_peer_reduce (one kernel per GPU "
+                         "over NVLink peer memory, csrc/peer.cu)")
     ap.add_argument("--no-trace-events", action="store_true",
                     help="diagnostic: timed region without the per-launch event pairs (the roofline object is then meaningless)")
     args = ap.parse_args()

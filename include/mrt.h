@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define MRT_VERSION 102
+#define MRT_VERSION 103
 
 enum {
     MRT_OK = 0,
@@ -168,6 +168,35 @@ int mrt_set_pipeline(mrt_ctx* ctx, uint32_t pipeline);
  * under MRT_PROFILE_TRACE_TIME, and what a kernel profiler needs (ncu cannot see kernel nodes of conditional graphs). */
 enum { MRT_SCHEDULE_GRAPH = 0, MRT_SCHEDULE_HOST_LOOP = 1 };
 int mrt_set_wave_schedule(mrt_ctx* ctx, uint32_t schedule);
+
+/* ---- framebuffer reduction over NVLink peer memory (the reference is single-device) -----------------
+ * Sample sharding leaves one SUM image per GPU (MRT_ACCUM_SUM); the job's image is scale * (their sum).  Instead of
+ * copy + ncclAllReduce + scale, every rank enqueues ONE kernel on its ctx stream that waits (flags in peer memory) until
+ * all ranks' images are complete, sums its 1/N slice of the pixels straight out of the peers' memory in rank order
+ * (deterministic: every rank, every run, the same bits), scales and stores the slice into every rank's result buffer,
+ * and ends only when every peer is done with this rank's image (csrc/peer.cu).  No NCCL, no host synchronisation.
+ *   mrt_peer_export    fills the handle other ranks need (raw pointers for ranks in the same process, CUDA IPC handles
+ *                      for ranks in other processes); allocates this ctx's flag block + result buffer on first use.
+ *   mrt_peer_connect   handles[world] in rank order, handles[rank] being this ctx's own.  Every rank must have
+ *                      connected before any rank reduces (barrier in the caller).  mrt_resize drops the connection.
+ *   mrt_peer_reduce    asynchronous; all ranks call it once per step, in the same order.
+ *   mrt_peer_result    this rank's copy of the reduced image (same bits on every rank).
+ *   mrt_peer_status    synchronises the ctx stream; MRT_E_STATE if a wait gave up (~2 s without the peer showing up). */
+#define MRT_PEER_MAX_RANKS 16
+typedef struct mrt_peer_handle {
+    unsigned char image_ipc[64], block_ipc[64];   /* cudaIpcMemHandle_t of the SUM image and of the exchange block */
+    uint64_t image_ptr, block_ptr;                /* the same two as device pointers, valid inside the exporting process */
+    int64_t pid;
+    int32_t device;
+    uint32_t width, height, ipc_valid;
+} mrt_peer_handle;
+int mrt_peer_export(mrt_ctx* ctx, mrt_peer_handle* out);
+int mrt_peer_connect(mrt_ctx* ctx, uint32_t rank, uint32_t world, const mrt_peer_handle* handles);
+int mrt_peer_reduce(mrt_ctx* ctx, float scale);
+int mrt_peer_result(mrt_ctx* ctx, void** device_ptr, size_t* bytes);
+int mrt_peer_status(mrt_ctx* ctx);
+int mrt_peer_read_result(mrt_ctx* ctx, float* rgba);   /* mrt_peer_status, then width * height * 4 floats to the host */
+int mrt_peer_disconnect(mrt_ctx* ctx);
 
 /* ---- optics extension: SURVEY.md 8(f4), BEYOND THE REFERENCE ------------------------------------------------------------
  * Nothing here has a counterpart in the reference, so nothing here can be pinned against it: the checker is the same

@@ -85,6 +85,7 @@ struct mrt_ctx {
     cudaEvent_t pollEvents[4] = {};                              // polling host loop: one event every 8 waves
     uint64_t graphKernels = 0; uint32_t kernelsPerWave = 2;      // kernels launched by graph replays (read back in mrt_get_stats)
     mrt_stats stats{};
+    void* peer = nullptr;                                        // csrc/peer.cu (mrt_peer_*): exchange block + peer mappings
 
     Grid2D grid() const { Grid2D g; g.W = W; g.H = H; g.rowFirst = rowFirst; g.rowStride = rowStride; return g; }
     uint32_t ownedRows() const { return rowFirst < H ? (H - rowFirst + rowStride - 1) / rowStride : 0; }
@@ -99,6 +100,7 @@ static void free_scene(mrt_ctx* c) {
     c->haveScene = false;
 }
 static void free_sized(mrt_ctx* c) {
+    peer_release(&c->peer);                                      // peers map dImage: the group dies with it
     cudaFree(c->dRays); cudaFree(c->dLightRays); cudaFree(c->dIsects); cudaFree(c->dImage); cudaFree(c->wfArena);
     c->dRays = nullptr; c->dLightRays = nullptr; c->dIsects = nullptr; c->dImage = nullptr; c->wfArena = nullptr;
     const uint32_t* triSlot = c->wf.triSlot; const float4* triRecords = c->wf.triRecords;
@@ -1291,6 +1293,7 @@ bool ctx_view(mrt_ctx* c, CtxView& out) {
     if (!c) return false;
     out.S = c->S; out.stream = c->stream; out.device = c->cfg.device; out.haveScene = c->haveScene;
     out.kernelLaunches = &c->stats.kernel_launches;
+    out.image = c->dImage; out.W = c->W; out.H = c->H; out.peerSlot = &c->peer;
     return true;
 }
 int api_fail(int code, const char* fmt, ...) {

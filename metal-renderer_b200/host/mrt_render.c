@@ -13,10 +13,12 @@
  *                    ncclAllReduce(sum image -> result) over NVLink, then mrt_scale_buffer(result, 1/frames).
  *   --shard rows:    GPU g renders rows y % N == g of every frame with the reference's running mean;
  *                    mrt_pack_rows -> ncclAllGather -> mrt_unpack_rows.  Bit-identical to one GPU.
+ *   --reduce peer:   (samples) no NCCL at all: mrt_peer_reduce, one kernel per GPU that sums the images over NVLink peer
+ *                    memory in rank order, scales and publishes the result to every GPU (csrc/peer.cu).
  * The library itself never links NCCL.
  *
  * usage: mrt_render [--scene NAME|file.obj] [--size WxH] [--frames N] [--depth L] [--seed S] [--device D]
- *                   [--devices a,b,...] [--shard samples|rows]
+ *                   [--devices a,b,...] [--shard samples|rows] [--reduce nccl|peer]
  *                   [--pipeline auto|wavefront|fused|staged] [--out image.pfm]
  *                   [--tone] [--srgb]            presentation pass on the written image (Shaders.metal:43-51; one GPU)
  *                   [--resume file.ckpt]         continue an earlier render (frames then count from the stored index; one GPU)
@@ -53,7 +55,7 @@ static int write_pfm(const char* path, const float* rgba, unsigned w, unsigned h
 
 typedef struct options {
     const char* scene_name; const char* out; const char* resume; const char* checkpoint;
-    unsigned tone, srgb, w, h, frames, depth, pipeline, rows, optics;
+    unsigned tone, srgb, w, h, frames, depth, pipeline, rows, optics, peer;
     float spread;
     int devices[16]; int n_devices;
     unsigned long long seed;
@@ -64,8 +66,9 @@ typedef struct options {
 typedef struct worker {
     const options* opt; const mrt_prepared_scene* prepared; const float* tiles; const float* init;
     int rank, world; ncclComm_t comm; pthread_barrier_t* barrier;
+    mrt_peer_handle* handles;      /* --reduce peer: one per rank, shared by all workers */
     float* image;                  /* rank 0: host copy of the job's image */
-    mrt_stats stats; float device_ms, collective_ms; int rc, passed; char error[512];
+    mrt_stats stats; float device_ms, collective_ms; int rc, passed, barriers; char error[512];
 } worker;
 
 #define WCHECK(call) do { int rc_ = (call); if (rc_ != MRT_OK) { snprintf(w->error, sizeof w->error, "%s failed (%d): %s", #call, rc_, mrt_last_error()); \
@@ -80,7 +83,7 @@ static void* worker_main(void* arg) {
     const options* o = w->opt;
     const unsigned N = (unsigned)w->world, g = (unsigned)w->rank;
     mrt_ctx* ctx = NULL;
-    void* result = NULL; void* send = NULL; void* recv = NULL; void* stream = NULL;
+    void* result = NULL; void* send = NULL; void* recv = NULL; void* stream = NULL; void* peer_result = NULL;
     void* image_dev = NULL; size_t image_bytes = 0;
     mrt_config cfg;
     mrt_config_default(&cfg);
@@ -104,7 +107,7 @@ static void* worker_main(void* arg) {
         WCUDA(cudaMalloc(&recv, shard_bytes * N));
         WNCCL(ncclAllGather(send, recv, 32, ncclFloat, w->comm, (cudaStream_t)stream));   /* untimed: NCCL sets its channels up on first use */
         WCHECK(mrt_sync(ctx));
-        pthread_barrier_wait(w->barrier); w->passed = 1;
+        pthread_barrier_wait(w->barrier); w->passed++;
         WCHECK(mrt_event_record(ctx, 0));
         WCHECK(mrt_render_frames(ctx, 0, o->frames, 1, w->tiles));            /* every frame, owned rows only */
         WCHECK(mrt_pack_rows(ctx, send));
@@ -119,25 +122,40 @@ static void* worker_main(void* arg) {
          * (slot f%3 is refreshed at frame f, bounce i reads slot (f+i)%3: Renderer.mm:492-496, 538) */
         const unsigned mine = o->frames > g ? (o->frames - g + N - 1) / N : 0;
         for (unsigned f = g >= 2 ? g - 2 : 0; f < g; ++f) WCHECK(mrt_set_noise(ctx, f % 3, w->tiles + (size_t)f * MRT_NOISE_TILE_FLOATS));
-        WCUDA(cudaMalloc(&result, image_bytes));
-        WNCCL(ncclAllReduce(result, result, 32, ncclFloat, ncclSum, w->comm, (cudaStream_t)stream));   /* untimed: first-use set-up */
+        if (o->peer) {                                  /* one kernel per GPU over NVLink peer memory instead of NCCL (csrc/peer.cu) */
+            WCHECK(mrt_peer_export(ctx, &w->handles[g]));
+            pthread_barrier_wait(w->barrier); w->passed++;                 /* every handle is there */
+            WCHECK(mrt_peer_connect(ctx, g, N, w->handles));
+            pthread_barrier_wait(w->barrier); w->passed++;                 /* nobody reduces before everybody has connected */
+            WCHECK(mrt_peer_result(ctx, &peer_result, NULL));
+        } else {
+            WCUDA(cudaMalloc(&result, image_bytes));
+            WNCCL(ncclAllReduce(result, result, 32, ncclFloat, ncclSum, w->comm, (cudaStream_t)stream));   /* untimed: first-use set-up */
+        }
         WCHECK(mrt_sync(ctx));
-        pthread_barrier_wait(w->barrier); w->passed = 1;
+        pthread_barrier_wait(w->barrier); w->passed++;
         WCHECK(mrt_event_record(ctx, 0));
         if (mine) WCHECK(mrt_render_frames(ctx, g, mine, N, w->tiles + (size_t)g * MRT_NOISE_TILE_FLOATS));
         WCHECK(mrt_event_record(ctx, 1));
-        WNCCL(ncclAllReduce(image_dev, result, pixels * 4, ncclFloat, ncclSum, w->comm, (cudaStream_t)stream));
-        WCHECK(mrt_event_record(ctx, 2));
-        WCHECK(mrt_scale_buffer(ctx, result, pixels, 1.0f / (float)o->frames));
-        WCHECK(mrt_event_record(ctx, 3));
-        WCHECK(mrt_sync(ctx));
-        if (g == 0) WCUDA(cudaMemcpy(w->image, result, image_bytes, cudaMemcpyDeviceToHost));
+        if (o->peer) {
+            WCHECK(mrt_peer_reduce(ctx, 1.0f / (float)o->frames));
+            WCHECK(mrt_event_record(ctx, 2));
+            WCHECK(mrt_event_record(ctx, 3));
+            WCHECK(mrt_peer_status(ctx));                                  /* synchronises; a wait that gave up is an error */
+        } else {
+            WNCCL(ncclAllReduce(image_dev, result, pixels * 4, ncclFloat, ncclSum, w->comm, (cudaStream_t)stream));
+            WCHECK(mrt_event_record(ctx, 2));
+            WCHECK(mrt_scale_buffer(ctx, result, pixels, 1.0f / (float)o->frames));
+            WCHECK(mrt_event_record(ctx, 3));
+            WCHECK(mrt_sync(ctx));
+        }
+        if (g == 0) WCUDA(cudaMemcpy(w->image, o->peer ? peer_result : result, image_bytes, cudaMemcpyDeviceToHost));
     }
     WCHECK(mrt_event_elapsed_ms(ctx, 0, 3, &w->device_ms));
     WCHECK(mrt_event_elapsed_ms(ctx, 1, 2, &w->collective_ms));
     WCHECK(mrt_get_stats(ctx, &w->stats));
 done:
-    if (w->rc && !w->passed) pthread_barrier_wait(w->barrier);     /* never leave the others waiting at the start line */
+    while (w->rc && w->passed < w->barriers) { pthread_barrier_wait(w->barrier); w->passed++; }   /* never leave the others waiting */
     if (result) cudaFree(result);
     if (send) cudaFree(send);
     if (recv) cudaFree(recv);
@@ -151,9 +169,14 @@ static int render_multi(const options* o, const mrt_scene* scene, const mrt_scen
     double tb = now_s();
     CHECK(mrt_scene_prepare_from(scene, 0, &prepared));            /* both trees built once, on all host cores */
     double build_ms = (now_s() - tb) * 1e3;
+    const int use_peer = o->peer && !o->rows;
     ncclComm_t comms[16];
-    ncclResult_t nr = ncclCommInitAll(comms, N, o->devices);
-    if (nr != ncclSuccess) { fprintf(stderr, "ncclCommInitAll failed: %s\n", ncclGetErrorString(nr)); return 1; }
+    memset(comms, 0, sizeof comms);
+    mrt_peer_handle handles[16];
+    if (!use_peer) {
+        ncclResult_t nr = ncclCommInitAll(comms, N, o->devices);
+        if (nr != ncclSuccess) { fprintf(stderr, "ncclCommInitAll failed: %s\n", ncclGetErrorString(nr)); return 1; }
+    }
     const unsigned frames = o->frames ? o->frames : 1;
     float* tiles = (float*)malloc((size_t)frames * MRT_NOISE_TILE_FLOATS * sizeof(float));
     float* init = (float*)malloc(MRT_NOISE_TILE_FLOATS * sizeof(float));
@@ -168,13 +191,13 @@ static int render_multi(const options* o, const mrt_scene* scene, const mrt_scen
     double t0 = now_s();
     for (int g = 0; g < N; ++g) {
         ws[g].opt = o; ws[g].prepared = prepared; ws[g].tiles = tiles; ws[g].init = init; ws[g].rank = g; ws[g].world = N;
-        ws[g].comm = comms[g]; ws[g].barrier = &barrier; ws[g].image = image;
+        ws[g].comm = comms[g]; ws[g].barrier = &barrier; ws[g].image = image; ws[g].handles = handles; ws[g].barriers = use_peer ? 3 : 1;
         pthread_create(&th[g], NULL, worker_main, &ws[g]);
     }
     int failed = 0;
     for (int g = 0; g < N; ++g) { pthread_join(th[g], NULL); if (ws[g].rc) { fprintf(stderr, "device %d: %s\n", o->devices[g], ws[g].error); failed = 1; } }
     double t1 = now_s();
-    for (int g = 0; g < N; ++g) ncclCommDestroy(comms[g]);
+    for (int g = 0; g < N && !use_peer; ++g) ncclCommDestroy(comms[g]);
     pthread_barrier_destroy(&barrier);
     if (failed) return 1;
     float ms = 0, coll = 0; unsigned long long primary = 0, shadow = 0, launches = 0;
@@ -185,9 +208,9 @@ static int render_multi(const options* o, const mrt_scene* scene, const mrt_scen
     }
     double samples = (double)o->w * o->h * o->frames;
     printf("{\"scene\": \"%s\", \"triangles\": %u, \"lights\": %u, \"width\": %u, \"height\": %u, \"frames\": %u, \"depth\": %u, "
-           "\"gpus\": %d, \"shard\": \"%s\", \"device_ms\": %.3f, \"collective_ms\": %.3f, \"wall_ms\": %.3f, \"msamples_per_s\": %.2f, "
+           "\"gpus\": %d, \"shard\": \"%s\", \"reduce\": \"%s\", \"device_ms\": %.3f, \"collective_ms\": %.3f, \"wall_ms\": %.3f, \"msamples_per_s\": %.2f, "
            "\"mrays_per_s\": %.2f, \"primary_rays\": %llu, \"shadow_rays\": %llu, \"kernel_launches\": %llu, \"scene_prepare_ms\": %.1f}\n",
-           o->scene_name, view->triangle_count, view->light_count, o->w, o->h, o->frames, o->depth, N, o->rows ? "rows" : "samples",
+           o->scene_name, view->triangle_count, view->light_count, o->w, o->h, o->frames, o->depth, N, o->rows ? "rows" : "samples", o->rows ? "nccl all-gather" : (use_peer ? "peer kernel" : "nccl all-reduce"),
            ms, coll, (t1 - t0) * 1e3, samples / (ms * 1e3), (double)(primary + shadow) / (ms * 1e3), primary, shadow, launches, build_ms);
     if (o->out && write_pfm(o->out, image, o->w, o->h)) { fprintf(stderr, "cannot write %s\n", o->out); return 1; }
     free(tiles); free(init); free(image);
@@ -218,6 +241,7 @@ int main(int argc, char** argv) {
             ++i;
         }
         else if (!strcmp(a, "--shard")) { o.rows = !strcmp(v, "rows"); if (!o.rows && strcmp(v, "samples")) { fprintf(stderr, "bad --shard\n"); return 2; } ++i; }
+        else if (!strcmp(a, "--reduce")) { o.peer = !strcmp(v, "peer"); if (!o.peer && strcmp(v, "nccl")) { fprintf(stderr, "bad --reduce\n"); return 2; } ++i; }
         else if (!strcmp(a, "--pipeline")) {
             o.pipeline = !strcmp(v, "staged") ? MRT_PIPELINE_STAGED : !strcmp(v, "fused") ? MRT_PIPELINE_MEGAKERNEL
                        : !strcmp(v, "wavefront") ? MRT_PIPELINE_WAVEFRONT : MRT_PIPELINE_AUTO;

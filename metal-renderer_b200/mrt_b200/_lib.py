@@ -59,6 +59,14 @@ class Stats(C.Structure):
                 ("tail_waves", C.c_uint32), ("reserved", C.c_uint32)]
 
 
+class PeerHandle(C.Structure):      # mrt_peer_handle (include/mrt.h)
+    _fields_ = [("image_ipc", C.c_ubyte * 64), ("block_ipc", C.c_ubyte * 64), ("image_ptr", C.c_uint64), ("block_ptr", C.c_uint64),
+                ("pid", C.c_int64), ("device", C.c_int32), ("width", C.c_uint32), ("height", C.c_uint32), ("ipc_valid", C.c_uint32)]
+
+
+PEER_MAX_RANKS = 16
+
+
 class SceneView(C.Structure):
     _fields_ = [("vertices", C.c_void_p), ("vertex_count", C.c_uint32),
                 ("indices", C.c_void_p), ("triangle_count", C.c_uint32),
@@ -106,6 +114,13 @@ SIGNATURES = {
     "mrt_set_pipeline": (C.c_int, [_P, _U32]),
     "mrt_set_wave_schedule": (C.c_int, [_P, _U32]),
     "mrt_set_extensions": (C.c_int, [_P, _U32, C.c_float]),
+    "mrt_peer_export": (C.c_int, [_P, _P]),
+    "mrt_peer_connect": (C.c_int, [_P, _U32, _U32, _P]),
+    "mrt_peer_reduce": (C.c_int, [_P, C.c_float]),
+    "mrt_peer_result": (C.c_int, [_P, _P, _P]),
+    "mrt_peer_status": (C.c_int, [_P]),
+    "mrt_peer_read_result": (C.c_int, [_P, _P]),
+    "mrt_peer_disconnect": (C.c_int, [_P]),
     "mrt_build_alias_table": (C.c_int, [_P, _U32, _P, _P]),
     "mrt_set_profile": (C.c_int, [_P, _U32]),
     "mrt_raygen": (C.c_int, [_P, _U32]),

@@ -65,6 +65,16 @@ class TorchCollective:
         import torch.distributed as dist
         dist.all_gather_into_tensor(out, inp)
 
+    def all_gather_object(self, obj):
+        import torch.distributed as dist
+        out = [None] * dist.get_world_size()
+        dist.all_gather_object(out, obj)
+        return out
+
+    def barrier(self):
+        import torch.distributed as dist
+        dist.barrier()
+
 
 class CudaEndpoint:
     """The CUDA Renderer as ShardedRenderer sees it.  torch is plumbing here: it owns the reduce / gather buffers and
@@ -88,6 +98,14 @@ class CudaEndpoint:
 
     def new_buffer(self, floats):
         return self.torch.empty(floats, dtype=self.torch.float32, device=f"cuda:{self.device}")
+
+    def peer_result(self):
+        """The result buffer of the peer-memory reduction (csrc/peer.cu) as a tensor aliasing it."""
+        ptr, nbytes = self.r.peer_result_ptr()
+
+        class _Buf:
+            __cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+        return self.torch.as_tensor(_Buf(), device=f"cuda:{self.device}")
 
     def image_to(self, buf):
         with self.stream():
@@ -125,10 +143,17 @@ class CudaEndpoint:
 class ShardedRenderer:
     """Drives one rank's renderer and the per-step collective; see the module docstring for the two modes."""
 
-    def __init__(self, endpoint, rank, world, collective=None, mode="samples"):
+    def __init__(self, endpoint, rank, world, collective=None, mode="samples", reduce="collective"):
+        """reduce (samples mode): "collective" = copy + all-reduce (NCCL) + scale; "peer" = ONE kernel per rank that sums
+        the ranks' images over NVLink peer memory (mrt_peer_reduce, csrc/peer.cu) — the collective is then only used
+        once, to exchange the handles."""
         if mode not in ("samples", "rows"):
             raise ValueError("mode must be 'samples' or 'rows'")
+        reduce = "collective" if reduce == "nccl" else reduce
+        if reduce not in ("collective", "peer"):
+            raise ValueError("reduce must be 'collective' or 'peer'")
         self.ep, self.rank, self.world, self.mode = endpoint, rank, world, mode
+        self.reduce = reduce if (world > 1 and mode == "samples") else "collective"
         self.coll = collective or TorchCollective()
         self.next_frame = 0
         self.total_frames = 0
@@ -138,7 +163,20 @@ class ShardedRenderer:
         if world > 1:
             if mode == "samples":
                 endpoint.r.set_accumulate_mode(L.ACCUM_SUM)
-                self.result = endpoint.new_buffer(endpoint.r.width * endpoint.r.height * 4)
+                if self.reduce == "peer":
+                    handles = self.coll.all_gather_object(endpoint.r.peer_export())
+                    try:
+                        endpoint.r.peer_connect(rank, world, handles)
+                        err = None
+                    except Exception as e:                  # noqa: BLE001 — every rank must reach the exchange below
+                        err = f"rank {rank}: {e}"
+                    # doubles as the barrier: nobody reduces before everybody has connected, and all ranks fail together
+                    errs = [e for e in self.coll.all_gather_object(err) if e]
+                    if errs:
+                        raise RuntimeError("peer-memory reduction unavailable: " + "; ".join(errs))
+                    self.result = endpoint.peer_result()
+                else:
+                    self.result = endpoint.new_buffer(endpoint.r.width * endpoint.r.height * 4)
             else:
                 endpoint.r.set_row_shard(rank, world)
                 _, floats = endpoint.shard_layout(world)
@@ -160,14 +198,21 @@ class ShardedRenderer:
                 if lead_in is not None and f in lead_in:
                     ep.load_noise(f % 3, lead_in[f])
             r.draw(plan.n_frames, noise_tiles, first_frame=plan.first_frame, frame_stride=plan.frame_stride, sync=False)
-            ep.image_to(self.result)                      # the rank's own sum keeps growing; the reduce works on a copy
-            if self.time_events:
-                r.event_record(self.time_events[0])
-            with ep.stream():
-                self.coll.all_reduce(self.result)
-            if self.time_events:
-                r.event_record(self.time_events[1])
-            ep.scale(self.result, 1.0 / (self.total_frames + plan.total_frames))
+            if self.reduce == "peer":                     # one kernel: wait for the peers, sum over NVLink, scale, publish
+                if self.time_events:
+                    r.event_record(self.time_events[0])
+                r.peer_reduce(1.0 / (self.total_frames + plan.total_frames))
+                if self.time_events:
+                    r.event_record(self.time_events[1])
+            else:
+                ep.image_to(self.result)                  # the rank's own sum keeps growing; the reduce works on a copy
+                if self.time_events:
+                    r.event_record(self.time_events[0])
+                with ep.stream():
+                    self.coll.all_reduce(self.result)
+                if self.time_events:
+                    r.event_record(self.time_events[1])
+                ep.scale(self.result, 1.0 / (self.total_frames + plan.total_frames))
         else:
             plan = FramePlan(self.next_frame, frames_per_rank, 1, frames_per_rank, frames_per_rank)
             r.draw(frames_per_rank, noise_tiles, first_frame=plan.first_frame, frame_stride=1, sync=False)

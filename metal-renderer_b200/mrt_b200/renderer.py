@@ -203,6 +203,41 @@ class Renderer:
         L.check(L.lib().mrt_stream_handle(self._ctx, C.byref(p)))
         return p.value or 0
 
+    # ---- framebuffer reduction over NVLink peer memory (csrc/peer.cu; no NCCL) ----------------------------
+    def peer_export(self):
+        """This ctx's handle as bytes (ctypes.sizeof(PeerHandle)); give every rank the handles of all ranks."""
+        h = L.PeerHandle()
+        L.check(L.lib().mrt_peer_export(self._ctx, C.byref(h)))
+        return bytes(h)
+
+    def peer_connect(self, rank, world, handles):
+        """handles: `world` byte strings from peer_export in rank order.  Barrier between ranks before the first reduce."""
+        arr = (L.PeerHandle * world)()
+        for i, b in enumerate(handles):
+            C.memmove(C.byref(arr[i]), bytes(b), C.sizeof(L.PeerHandle))
+        L.check(L.lib().mrt_peer_connect(self._ctx, rank, world, arr))
+
+    def peer_reduce(self, scale):
+        """Asynchronous: result = scale * sum over ranks of the SUM images, in every rank's result buffer."""
+        L.check(L.lib().mrt_peer_reduce(self._ctx, scale))
+
+    def peer_result_ptr(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        L.check(L.lib().mrt_peer_result(self._ctx, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def peer_result(self):
+        """Synchronises and returns the reduced image as (H, W, 4) float32."""
+        out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        L.check(L.lib().mrt_peer_read_result(self._ctx, L.ptr(out)))
+        return out
+
+    def peer_status(self):
+        L.check(L.lib().mrt_peer_status(self._ctx))
+
+    def peer_disconnect(self):
+        L.check(L.lib().mrt_peer_disconnect(self._ctx))
+
     def scale_buffer(self, device_address, pixels, scale):
         """rgb *= scale, alpha = 1 on a device buffer of `pixels` float4 (the reduced sum image)."""
         L.check(L.lib().mrt_scale_buffer(self._ctx, C.c_void_p(int(device_address)), pixels, scale))

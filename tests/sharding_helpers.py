@@ -126,6 +126,12 @@ class _LocalCollective:
         t.copy_(total)
         torch.cuda.synchronize()
 
+    def all_gather_object(self, obj):
+        return self._exchange(obj)
+
+    def barrier(self):
+        self.g.barrier.wait()
+
     def all_gather(self, out, inp):
         import torch
         parts = [p.clone() for p in self._exchange(inp)]

@@ -27,7 +27,9 @@ def _rank(rank, world, group, mode, frames_per_rank, scene, out, errors):
         for s in range(3):
             r.update_noise(s, init)
         ep = D.CudaEndpoint(r, 0)
-        sr = D.ShardedRenderer(ep, rank, world, group.collective(rank, ep), mode=mode)
+        reduce = "peer" if mode == "samples-peer" else "collective"
+        mode = "samples" if mode == "samples-peer" else mode
+        sr = D.ShardedRenderer(ep, rank, world, group.collective(rank, ep), mode=mode, reduce=reduce)
         for step in range(STEPS):
             lead = None
             if mode == "samples":
@@ -37,14 +39,17 @@ def _rank(rank, world, group, mode, frames_per_rank, scene, out, errors):
             else:
                 tiles = m.noise_tiles(SEED, sr.next_frame, frames_per_rank)
             sr.step(frames_per_rank, tiles, lead_in=lead, sync=True)
+            if reduce == "peer":
+                r.peer_status()                             # a wait that gave up is an error, not an image
             out[(rank, step)] = ep.read(sr.output()).copy()
+        group.barrier.wait()                                # nobody frees buffers a peer may still map
         r.close()
     except Exception as e:              # noqa: BLE001 — reported by the main thread
         errors.append((rank, repr(e)))
         group.barrier.abort()
 
 
-@pytest.mark.parametrize("mode,world", [("rows", 2), ("rows", 3), ("samples", 2), ("samples", 3)])
+@pytest.mark.parametrize("mode,world", [("rows", 2), ("rows", 3), ("samples", 2), ("samples", 3), ("samples-peer", 2), ("samples-peer", 3)])
 def test_sharded_step_on_one_gpu_matches_the_sequential_oracle(mode, world):
     scene = m.Scene.procedural("cornell-water", 0)
     frames_per_rank = 3
@@ -56,7 +61,7 @@ def test_sharded_step_on_one_gpu_matches_the_sequential_oracle(mode, world):
         t.join(timeout=600)
     assert not errors, errors
     for step in range(STEPS):
-        frames = (step + 1) * frames_per_rank * (world if mode == "samples" else 1)
+        frames = (step + 1) * frames_per_rank * (world if mode != "rows" else 1)
         want = sequential_oracle_image(scene, W, H, L, SEED, frames)
         for g in range(world):
             got = out[(g, step)]
