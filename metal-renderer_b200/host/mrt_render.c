@@ -68,7 +68,7 @@ typedef struct worker {
     int rank, world; ncclComm_t comm; pthread_barrier_t* barrier;
     mrt_peer_handle* handles;      /* --reduce peer: one per rank, shared by all workers */
     float* image;                  /* rank 0: host copy of the job's image */
-    mrt_stats stats; float device_ms, collective_ms; int rc, passed, barriers; char error[512];
+    mrt_stats stats; float device_ms, collective_ms; double setup_ms, teardown_ms; int rc, passed, barriers; char error[512];
 } worker;
 
 #define WCHECK(call) do { int rc_ = (call); if (rc_ != MRT_OK) { snprintf(w->error, sizeof w->error, "%s failed (%d): %s", #call, rc_, mrt_last_error()); \
@@ -86,6 +86,7 @@ static void* worker_main(void* arg) {
     void* result = NULL; void* send = NULL; void* recv = NULL; void* stream = NULL; void* peer_result = NULL;
     void* image_dev = NULL; size_t image_bytes = 0;
     mrt_config cfg;
+    const double t_start = now_s();
     mrt_config_default(&cfg);
     cfg.device = o->devices[g];
     cfg.max_path_length = o->depth;
@@ -108,6 +109,7 @@ static void* worker_main(void* arg) {
         WNCCL(ncclAllGather(send, recv, 32, ncclFloat, w->comm, (cudaStream_t)stream));   /* untimed: NCCL sets its channels up on first use */
         WCHECK(mrt_sync(ctx));
         pthread_barrier_wait(w->barrier); w->passed++;
+        w->setup_ms = (now_s() - t_start) * 1e3;
         WCHECK(mrt_event_record(ctx, 0));
         WCHECK(mrt_render_frames(ctx, 0, o->frames, 1, w->tiles));            /* every frame, owned rows only */
         WCHECK(mrt_pack_rows(ctx, send));
@@ -134,6 +136,7 @@ static void* worker_main(void* arg) {
         }
         WCHECK(mrt_sync(ctx));
         pthread_barrier_wait(w->barrier); w->passed++;
+        w->setup_ms = (now_s() - t_start) * 1e3;
         WCHECK(mrt_event_record(ctx, 0));
         if (mine) WCHECK(mrt_render_frames(ctx, g, mine, N, w->tiles + (size_t)g * MRT_NOISE_TILE_FLOATS));
         WCHECK(mrt_event_record(ctx, 1));
@@ -156,10 +159,14 @@ static void* worker_main(void* arg) {
     WCHECK(mrt_get_stats(ctx, &w->stats));
 done:
     while (w->rc && w->passed < w->barriers) { pthread_barrier_wait(w->barrier); w->passed++; }   /* never leave the others waiting */
-    if (result) cudaFree(result);
-    if (send) cudaFree(send);
-    if (recv) cudaFree(recv);
-    if (ctx) mrt_destroy(ctx);
+    {
+        const double t_end = now_s();
+        if (result) cudaFree(result);
+        if (send) cudaFree(send);
+        if (recv) cudaFree(recv);
+        if (ctx) mrt_destroy(ctx);
+        w->teardown_ms = (now_s() - t_end) * 1e3;
+    }
     return NULL;
 }
 
@@ -201,7 +208,10 @@ static int render_multi(const options* o, const mrt_scene* scene, const mrt_scen
     pthread_barrier_destroy(&barrier);
     if (failed) return 1;
     float ms = 0, coll = 0; unsigned long long primary = 0, shadow = 0, launches = 0;
+    double setup = 0, teardown = 0;
     for (int g = 0; g < N; ++g) {
+        if (ws[g].setup_ms > setup) setup = ws[g].setup_ms;
+        if (ws[g].teardown_ms > teardown) teardown = ws[g].teardown_ms;
         if (ws[g].device_ms > ms) ms = ws[g].device_ms;
         if (ws[g].collective_ms > coll) coll = ws[g].collective_ms;
         primary += ws[g].stats.primary_rays; shadow += ws[g].stats.shadow_rays; launches += ws[g].stats.kernel_launches;
@@ -209,9 +219,9 @@ static int render_multi(const options* o, const mrt_scene* scene, const mrt_scen
     double samples = (double)o->w * o->h * o->frames;
     printf("{\"scene\": \"%s\", \"triangles\": %u, \"lights\": %u, \"width\": %u, \"height\": %u, \"frames\": %u, \"depth\": %u, "
            "\"gpus\": %d, \"shard\": \"%s\", \"reduce\": \"%s\", \"device_ms\": %.3f, \"collective_ms\": %.3f, \"wall_ms\": %.3f, \"msamples_per_s\": %.2f, "
-           "\"mrays_per_s\": %.2f, \"primary_rays\": %llu, \"shadow_rays\": %llu, \"kernel_launches\": %llu, \"scene_prepare_ms\": %.1f}\n",
+           "\"mrays_per_s\": %.2f, \"primary_rays\": %llu, \"shadow_rays\": %llu, \"kernel_launches\": %llu, \"scene_prepare_ms\": %.1f, \"rank_setup_ms\": %.1f, \"rank_teardown_ms\": %.1f}\n",
            o->scene_name, view->triangle_count, view->light_count, o->w, o->h, o->frames, o->depth, N, o->rows ? "rows" : "samples", o->rows ? "nccl all-gather" : (use_peer ? "peer kernel" : "nccl all-reduce"),
-           ms, coll, (t1 - t0) * 1e3, samples / (ms * 1e3), (double)(primary + shadow) / (ms * 1e3), primary, shadow, launches, build_ms);
+           ms, coll, (t1 - t0) * 1e3, samples / (ms * 1e3), (double)(primary + shadow) / (ms * 1e3), primary, shadow, launches, build_ms, setup, teardown);
     if (o->out && write_pfm(o->out, image, o->w, o->h)) { fprintf(stderr, "cannot write %s\n", o->out); return 1; }
     free(tiles); free(init); free(image);
     mrt_prepared_scene_destroy(prepared);

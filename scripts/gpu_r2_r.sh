@@ -19,9 +19,9 @@ python scripts/compare_pfm.py gpurun_out/r_peer_1.pfm gpurun_out/r_nccl_1.pfm
 python scripts/compare_pfm.py gpurun_out/r_peer_1.pfm gpurun_out/r_1gpu.pfm
 } 2>&1 | tee gpurun_out/r_c_driver_${N}gpu.log
 rm -f gpurun_out/r_*.pfm
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 5 --warmup 3 \
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N --steps 5 --warmup 3 --no-cpu-baseline \
   > gpurun_out/r_bench_${N}gpu_nccl.json 2> gpurun_out/r_bench_${N}gpu_nccl.err; tail -c 900 gpurun_out/r_bench_${N}gpu_nccl.json; tail -3 gpurun_out/r_bench_${N}gpu_nccl.err
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 bench.py --gpus $N --steps 5 --warmup 3 --reduce peer --no-cpu-baseline \
+[ "$N" -le 2 ] && timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 bench.py --gpus $N --steps 5 --warmup 3 --reduce peer --no-cpu-baseline \
   > gpurun_out/r_bench_${N}gpu_peer.json 2> gpurun_out/r_bench_${N}gpu_peer.err; tail -c 900 gpurun_out/r_bench_${N}gpu_peer.json; tail -3 gpurun_out/r_bench_${N}gpu_peer.err
 python - <<PY
 import json
