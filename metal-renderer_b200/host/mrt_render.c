@@ -130,6 +130,8 @@ static void* worker_main(void* arg) {
             WCHECK(mrt_peer_connect(ctx, g, N, w->handles));
             pthread_barrier_wait(w->barrier); w->passed++;                 /* nobody reduces before everybody has connected */
             WCHECK(mrt_peer_result(ctx, &peer_result, NULL));
+            WCHECK(mrt_peer_reduce(ctx, 0.0f));             /* untimed, like NCCL's first call below: first touch of every peer's pages */
+            WCHECK(mrt_peer_status(ctx));
         } else {
             WCUDA(cudaMalloc(&result, image_bytes));
             WNCCL(ncclAllReduce(result, result, 32, ncclFloat, ncclSum, w->comm, (cudaStream_t)stream));   /* untimed: first-use set-up */
