@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define MRT_VERSION 103
+#define MRT_VERSION 104
 
 enum {
     MRT_OK = 0,
@@ -171,26 +171,31 @@ int mrt_set_wave_schedule(mrt_ctx* ctx, uint32_t schedule);
 
 /* ---- framebuffer reduction over NVLink peer memory (the reference is single-device) -----------------
  * Sample sharding leaves one SUM image per GPU (MRT_ACCUM_SUM); the job's image is scale * (their sum).  Instead of
- * copy + ncclAllReduce + scale, every rank enqueues ONE kernel on its ctx stream that waits (flags in peer memory) until
- * all ranks' images are complete, sums its 1/N slice of the pixels straight out of the peers' memory in rank order
- * (deterministic: every rank, every run, the same bits), scales and stores the slice into every rank's result buffer,
- * and ends only when every peer is done with this rank's image (csrc/peer.cu).  No NCCL, no host synchronisation.
- *   mrt_peer_export    fills the handle other ranks need (raw pointers for ranks in the same process, CUDA IPC handles
- *                      for ranks in other processes); allocates this ctx's flag block + result buffer on first use.
+ * copy + ncclAllReduce + scale, every rank enqueues ONE kernel on its ctx stream that pushes slice g of its image into
+ * rank g's exchange block over NVLink, waits (flags in peer memory) until all ranks have pushed, sums its own slice in
+ * rank order (deterministic: every rank, every run, the same bits), scales, stores the slice into every rank's result
+ * image, and ends only when every peer has done the same (csrc/peer.cu).  No NCCL, no host synchronisation; peers only
+ * ever touch a rank's exchange block, never its SUM image.
+ *   mrt_peer_export    allocates this ctx's exchange block (flags + result + staging, 2 x the image) and fills the
+ *                      handle the other ranks need.  sharing = MRT_PEER_SHARE_PROCESS: all ranks live in this process
+ *                      (one thread per GPU): the block is mapped on every GPU through the driver's virtual memory
+ *                      management, no cudaDeviceEnablePeerAccess.  MRT_PEER_SHARE_IPC: ranks are processes (torchrun):
+ *                      a cudaMalloc block with a CUDA IPC handle (also usable inside one process).
  *   mrt_peer_connect   handles[world] in rank order, handles[rank] being this ctx's own.  Every rank must have
- *                      connected before any rank reduces (barrier in the caller).  mrt_resize drops the connection.
+ *                      connected before any rank reduces (barrier in the caller).  mrt_resize drops block and connection.
  *   mrt_peer_reduce    asynchronous; all ranks call it once per step, in the same order.
  *   mrt_peer_result    this rank's copy of the reduced image (same bits on every rank).
  *   mrt_peer_status    synchronises the ctx stream; MRT_E_STATE if a wait gave up (~2 s without the peer showing up). */
 #define MRT_PEER_MAX_RANKS 16
+enum { MRT_PEER_SHARE_IPC = 0, MRT_PEER_SHARE_PROCESS = 1 };
 typedef struct mrt_peer_handle {
-    unsigned char image_ipc[64], block_ipc[64];   /* cudaIpcMemHandle_t of the SUM image and of the exchange block */
-    uint64_t image_ptr, block_ptr;                /* the same two as device pointers, valid inside the exporting process */
+    unsigned char block_ipc[64];                  /* cudaIpcMemHandle_t of the exchange block (ipc_valid) */
+    uint64_t block_ptr;                           /* the block as a device pointer, valid inside the exporting process */
     int64_t pid;
     int32_t device;
-    uint32_t width, height, ipc_valid;
+    uint32_t width, height, ipc_valid, mapped_everywhere, reserved;
 } mrt_peer_handle;
-int mrt_peer_export(mrt_ctx* ctx, mrt_peer_handle* out);
+int mrt_peer_export(mrt_ctx* ctx, uint32_t sharing, mrt_peer_handle* out);
 int mrt_peer_connect(mrt_ctx* ctx, uint32_t rank, uint32_t world, const mrt_peer_handle* handles);
 int mrt_peer_reduce(mrt_ctx* ctx, float scale);
 int mrt_peer_result(mrt_ctx* ctx, void** device_ptr, size_t* bytes);

@@ -125,13 +125,20 @@ static void* worker_main(void* arg) {
         const unsigned mine = o->frames > g ? (o->frames - g + N - 1) / N : 0;
         for (unsigned f = g >= 2 ? g - 2 : 0; f < g; ++f) WCHECK(mrt_set_noise(ctx, f % 3, w->tiles + (size_t)f * MRT_NOISE_TILE_FLOATS));
         if (o->peer) {                                  /* one kernel per GPU over NVLink peer memory instead of NCCL (csrc/peer.cu) */
-            WCHECK(mrt_peer_export(ctx, &w->handles[g]));
+            const double p0 = now_s();
+            WCHECK(mrt_peer_export(ctx, MRT_PEER_SHARE_PROCESS, &w->handles[g]));
+            const double p1 = now_s();
             pthread_barrier_wait(w->barrier); w->passed++;                 /* every handle is there */
+            const double p2 = now_s();
             WCHECK(mrt_peer_connect(ctx, g, N, w->handles));
+            const double p3 = now_s();
             pthread_barrier_wait(w->barrier); w->passed++;                 /* nobody reduces before everybody has connected */
             WCHECK(mrt_peer_result(ctx, &peer_result, NULL));
             WCHECK(mrt_peer_reduce(ctx, 0.0f));             /* untimed, like NCCL's first call below: first touch of every peer's pages */
             WCHECK(mrt_peer_status(ctx));
+            if (getenv("MRT_RENDER_VERBOSE"))
+                fprintf(stderr, "rank %u: before export %.1f ms, export %.1f, wait %.1f, connect %.1f, barrier + first reduce %.1f\n", g,
+                        (p0 - t_start) * 1e3, (p1 - p0) * 1e3, (p2 - p1) * 1e3, (p3 - p2) * 1e3, (now_s() - p3) * 1e3);
         } else {
             WCUDA(cudaMalloc(&result, image_bytes));
             WNCCL(ncclAllReduce(result, result, 32, ncclFloat, ncclSum, w->comm, (cudaStream_t)stream));   /* untimed: first-use set-up */

@@ -60,11 +60,13 @@ class Stats(C.Structure):
 
 
 class PeerHandle(C.Structure):      # mrt_peer_handle (include/mrt.h)
-    _fields_ = [("image_ipc", C.c_ubyte * 64), ("block_ipc", C.c_ubyte * 64), ("image_ptr", C.c_uint64), ("block_ptr", C.c_uint64),
-                ("pid", C.c_int64), ("device", C.c_int32), ("width", C.c_uint32), ("height", C.c_uint32), ("ipc_valid", C.c_uint32)]
+    _fields_ = [("block_ipc", C.c_ubyte * 64), ("block_ptr", C.c_uint64), ("pid", C.c_int64), ("device", C.c_int32),
+                ("width", C.c_uint32), ("height", C.c_uint32), ("ipc_valid", C.c_uint32), ("mapped_everywhere", C.c_uint32),
+                ("reserved", C.c_uint32)]
 
 
 PEER_MAX_RANKS = 16
+PEER_SHARE_IPC, PEER_SHARE_PROCESS = 0, 1
 
 
 class SceneView(C.Structure):
@@ -114,7 +116,7 @@ SIGNATURES = {
     "mrt_set_pipeline": (C.c_int, [_P, _U32]),
     "mrt_set_wave_schedule": (C.c_int, [_P, _U32]),
     "mrt_set_extensions": (C.c_int, [_P, _U32, C.c_float]),
-    "mrt_peer_export": (C.c_int, [_P, _P]),
+    "mrt_peer_export": (C.c_int, [_P, _U32, _P]),
     "mrt_peer_connect": (C.c_int, [_P, _U32, _U32, _P]),
     "mrt_peer_reduce": (C.c_int, [_P, C.c_float]),
     "mrt_peer_result": (C.c_int, [_P, _P, _P]),

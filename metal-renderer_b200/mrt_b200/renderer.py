@@ -204,10 +204,11 @@ class Renderer:
         return p.value or 0
 
     # ---- framebuffer reduction over NVLink peer memory (csrc/peer.cu; no NCCL) ----------------------------
-    def peer_export(self):
-        """This ctx's handle as bytes (ctypes.sizeof(PeerHandle)); give every rank the handles of all ranks."""
+    def peer_export(self, sharing=L.PEER_SHARE_IPC):
+        """This ctx's handle as bytes (ctypes.sizeof(PeerHandle)); give every rank the handles of all ranks.
+        sharing: PEER_SHARE_IPC (ranks are processes) or PEER_SHARE_PROCESS (all ranks are contexts of this process)."""
         h = L.PeerHandle()
-        L.check(L.lib().mrt_peer_export(self._ctx, C.byref(h)))
+        L.check(L.lib().mrt_peer_export(self._ctx, sharing, C.byref(h)))
         return bytes(h)
 
     def peer_connect(self, rank, world, handles):

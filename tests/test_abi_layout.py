@@ -74,4 +74,4 @@ def test_library_exports_every_declared_symbol():
     missing = [n for n in sorted(declared) if not hasattr(handle, n)]
     assert not missing, missing
     assert declared == set(L.SIGNATURES), declared ^ set(L.SIGNATURES)
-    assert handle.mrt_version() == 103
+    assert handle.mrt_version() == 104

@@ -1,6 +1,6 @@
 """mrt_peer_reduce (csrc/peer.cu): the sample-sharded framebuffer reduction as one kernel per rank over peer memory.
-On this one-GPU box the "peers" are several contexts on device 0 (same kernel, same flags protocol, local loads instead of
-NVLink ones); the two- and eight-GPU runs are in profiles/ (mrt_render --reduce peer, bench.py --reduce peer).
+On this one-GPU box the "peers" are several contexts on device 0 (same kernel, same flags protocol, local stores instead of
+NVLink ones; both kinds of exchange block: cudaMalloc + IPC handle, and the driver's virtual memory management); the two- and eight-GPU runs are in profiles/ (mrt_render --reduce peer, bench.py --reduce peer).
 The answer is defined exactly: scale * (((img0 + img1) + img2) ...) in fp32, alpha = 1, identical on every rank."""
 import numpy as np
 import pytest
@@ -10,7 +10,7 @@ import mrt_b200 as m
 pytestmark = pytest.mark.gpu
 
 
-def make_ranks(world, w, h, seed):
+def make_ranks(world, w, h, seed, sharing=m.PEER_SHARE_IPC):
     scene = m.Scene.procedural("cornell", 0)
     rng = np.random.default_rng(seed)
     ranks, images = [], []
@@ -20,7 +20,7 @@ def make_ranks(world, w, h, seed):
         img = rng.uniform(0.0, 50.0, (h, w, 4)).astype(np.float32)
         r.write_buffer(m.BUF_IMAGE, img)
         ranks.append(r); images.append(img)
-    handles = [r.peer_export() for r in ranks]
+    handles = [r.peer_export(sharing) for r in ranks]
     for g, r in enumerate(ranks):
         r.peer_connect(g, world, handles)
     return ranks, images
@@ -35,9 +35,10 @@ def expected(images, scale):
     return out
 
 
-@pytest.mark.parametrize("world,w,h", [(1, 17, 5), (2, 64, 36), (3, 33, 7), (5, 200, 101), (8, 320, 180)])
-def test_peer_reduce_is_the_rank_ordered_sum_on_every_rank(world, w, h):
-    ranks, images = make_ranks(world, w, h, seed=world)
+@pytest.mark.parametrize("sharing", [pytest.param(m.PEER_SHARE_IPC, id="cudaMalloc-block"), pytest.param(m.PEER_SHARE_PROCESS, id="vmm-block")])
+@pytest.mark.parametrize("world,w,h", [(1, 17, 5), (2, 64, 36), (3, 33, 7), (5, 200, 101), (8, 320, 180), (2, 1920, 1080)])
+def test_peer_reduce_is_the_rank_ordered_sum_on_every_rank(world, w, h, sharing):
+    ranks, images = make_ranks(world, w, h, seed=world, sharing=sharing)
     for step, scale in enumerate((0.25, 1.0 / 3.0)):
         if step == 1:                                        # the SUM images keep growing between steps
             for g, r in enumerate(ranks):
@@ -61,6 +62,8 @@ def test_peer_reduce_argument_and_state_errors():
     a = m.Renderer(device=0, max_path_length=2); a.init_raytracing(scene)
     with pytest.raises(m.MrtError, match="mrt_resize"):
         a.peer_export()
+    with pytest.raises(m.MrtError, match="sharing must be"):
+        a.peer_export(7)
     a.drawable_size_will_change(32, 16)
     with pytest.raises(m.MrtError, match="mrt_peer_connect first"):
         a.peer_reduce(1.0)
