@@ -559,8 +559,13 @@ def run_ours(args, wl):
             line["cpu_baseline"] = cpu_baseline(wl, m, scene)
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        try:
+            r.sync()
+            r.peer_disconnect()                         # let go of the peers' exchange blocks (CUDA IPC) before anybody frees its own
+        except Exception:                               # noqa: BLE001 — nothing was connected
+            pass
+        dist.barrier()                                  # from here on any rank may free its block (at interpreter exit: torch tensors
+        dist.destroy_process_group()                    # allocated on the ctx stream must die before the ctx does, so no r.close() here)
 
 
 def main():

@@ -185,7 +185,10 @@ int mrt_set_wave_schedule(mrt_ctx* ctx, uint32_t schedule);
  *                      connected before any rank reduces (barrier in the caller).  mrt_resize drops block and connection.
  *   mrt_peer_reduce    asynchronous; all ranks call it once per step, in the same order.
  *   mrt_peer_result    this rank's copy of the reduced image (same bits on every rank).
- *   mrt_peer_status    synchronises the ctx stream; MRT_E_STATE if a wait gave up (~2 s without the peer showing up). */
+ *   mrt_peer_status    synchronises the ctx stream; MRT_E_STATE if a wait gave up (~2 s without the peer showing up).
+ *   mrt_peer_disconnect closes this rank's mappings of its peers' blocks (its own block lives until mrt_resize /
+ *                      mrt_destroy).  Between processes: every rank disconnects, THEN a barrier, before any rank resizes
+ *                      or destroys its context — freeing exported memory under an importer is undefined in CUDA. */
 #define MRT_PEER_MAX_RANKS 16
 enum { MRT_PEER_SHARE_IPC = 0, MRT_PEER_SHARE_PROCESS = 1 };
 typedef struct mrt_peer_handle {

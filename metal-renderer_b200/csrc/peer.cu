@@ -229,15 +229,20 @@ int mrt_peer_export(mrt_ctx* ctx, uint32_t sharing, mrt_peer_handle* out) {
     cudaError_t e = cudaSetDevice(v.device);
     if (e == cudaSuccess) e = cudaStreamSynchronize(v.stream);
     if (e != cudaSuccess) return api_fail(MRT_E_CUDA, "mrt_peer_export: %s", cudaGetErrorString(e));
-    if (state_of(v)) peer_release(v.peerSlot);              // a fresh block every time: the two kinds of sharing allocate differently
-    PeerState* st = new PeerState();
-    *v.peerSlot = st;
-    st->pixels = v.W * v.H;
-    st->blockBytes = peer_block_bytes(st->pixels);
-    if (sharing == MRT_PEER_SHARE_PROCESS && !vmm_alloc(st, v.device, st->blockBytes)) sharing = MRT_PEER_SHARE_IPC;   // old driver: plain allocation,
-    if (!st->block) e = cudaMalloc(&st->block, st->blockBytes);                                                        // peers then need peer access
-    if (e == cudaSuccess) e = cudaMemset(st->block, 0, st->blockBytes);
-    if (e != cudaSuccess) { peer_release(v.peerSlot); return api_fail(MRT_E_CUDA, "mrt_peer_export: %s", cudaGetErrorString(e)); }
+    PeerState* st = state_of(v);
+    // An existing block of the same kind is handed out again: another process may still have it open through IPC, and
+    // freeing exported memory under an importer is undefined.  (A resize frees it: disconnect the peers first.)
+    if (st && (st->pixels != v.W * v.H || (st->mappedBytes != 0) != (sharing == MRT_PEER_SHARE_PROCESS && vmm().ok))) { peer_release(v.peerSlot); st = nullptr; }
+    if (!st) {
+        st = new PeerState();
+        *v.peerSlot = st;
+        st->pixels = v.W * v.H;
+        st->blockBytes = peer_block_bytes(st->pixels);
+        if (sharing == MRT_PEER_SHARE_PROCESS) vmm_alloc(st, v.device, st->blockBytes);      // an old driver falls through to a plain
+        if (!st->block) e = cudaMalloc(&st->block, st->blockBytes);                          // allocation: peers then need peer access
+        if (e == cudaSuccess) e = cudaMemset(st->block, 0, st->blockBytes);
+        if (e != cudaSuccess) { peer_release(v.peerSlot); return api_fail(MRT_E_CUDA, "mrt_peer_export: %s", cudaGetErrorString(e)); }
+    }
     std::memset(out, 0, sizeof *out);
     out->block_ptr = (uint64_t)(uintptr_t)st->block;
     out->pid = (int64_t)getpid(); out->device = v.device; out->width = v.W; out->height = v.H;
@@ -362,7 +367,7 @@ int mrt_peer_disconnect(mrt_ctx* ctx) {
     CtxView v;
     if (!ctx_view(ctx, v)) return api_fail(MRT_E_INVALID, "ctx is NULL");
     if (cudaSetDevice(v.device) == cudaSuccess) cudaStreamSynchronize(v.stream);
-    peer_release(v.peerSlot);
+    if (state_of(v)) peer_close(state_of(v));               // this rank's mappings of its peers' blocks; its own block stays
     return MRT_OK;
 }
 

@@ -230,6 +230,14 @@ class ShardedRenderer:
             r.sync()
         return plan
 
+    def close(self):
+        """Peer reduction between processes: every rank lets go of its peers' exchange blocks, then a barrier, so that no
+        rank frees (resize, destroy, exit) memory another process still has open."""
+        if self.reduce == "peer":
+            self.ep.r.peer_disconnect()
+            self.coll.barrier()
+            self.reduce = "closed"
+
     def output(self):
         """Device buffer holding the current image of the whole job: the reduced mean ('samples', world > 1) or the
         renderer's own image."""
