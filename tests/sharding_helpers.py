@@ -45,6 +45,38 @@ class _CheckerRenderer:
         self.o.set_row_shard(first, stride)
         self.first, self.stride = first, stride
 
+    # ---- stand-in for mrt_peer_* (csrc/peer.cu): same call sequence, the exchange done with torch.distributed ----------
+    fail_connect_on_rank = None          # set by a test: that rank's peer_connect raises
+
+    def peer_export(self, sharing=0):
+        self._exported = True
+        return b"checker-handle"
+
+    def peer_connect(self, rank, world, handles):
+        assert getattr(self, "_exported", False) and len(handles) == world and all(h == b"checker-handle" for h in handles)
+        if rank == self.fail_connect_on_rank:
+            raise RuntimeError("cannot map the memory of a peer (simulated)")
+        self._rank, self._world, self._connected = rank, world, True
+
+    def peer_reduce(self, scale):
+        import torch
+        import torch.distributed as dist
+        assert self._connected
+        mine = torch.from_numpy(self.o.read_buffer(3).reshape(-1).copy())
+        parts = [torch.empty_like(mine) for _ in range(self._world)]
+        dist.all_gather(parts, mine)
+        total = parts[0]
+        for p in parts[1:]:
+            total = total + p                                   # rank order, like k_peer_reduce
+        out = (total * np.float32(scale)).reshape(-1, 4)
+        out[:, 3] = 1.0
+        self._peer_result.copy_(out.reshape(-1))
+
+    def peer_status(self): pass
+
+    def peer_disconnect(self):
+        self._connected = False
+
 
 class CheckerEndpoint:
     """Endpoint over host tensors: image copies, pack / unpack and scale in numpy (the CUDA library's versions are
@@ -88,6 +120,11 @@ class CheckerEndpoint:
             n = len(range(g, self.h, shards))
             img[g::shards] = blocks[g, :n]
         self._set(img)
+
+    def peer_result(self):
+        import torch
+        self.r._peer_result = torch.zeros(self.w * self.h * 4, dtype=torch.float32)
+        return self.r._peer_result
 
     def load_noise(self, slot, tile): self.r.update_noise(slot, tile)
     def read(self, buf, host_tensor=None): return buf.numpy().reshape(self.h, self.w, 4).copy()

@@ -20,7 +20,17 @@ def _worker(rank, world, port, mode, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     ep = CheckerEndpoint(m.Scene.procedural("cornell", 0), W, H, L, SEED)
-    sr = D.ShardedRenderer(ep, rank, world, D.TorchCollective(), mode=mode)
+    reduce = "peer" if mode.startswith("samples-peer") else "collective"
+    if mode == "samples-peer-one-rank-cannot-connect":
+        ep.r.fail_connect_on_rank = 1
+        with pytest.raises(RuntimeError, match="peer-memory reduction unavailable: rank 1: cannot map"):     # on EVERY rank, together
+            D.ShardedRenderer(ep, rank, world, D.TorchCollective(), mode="samples", reduce="peer")
+        np.save(os.path.join(out_dir, f"{mode}_{rank}_raised.npy"), np.ones(1))
+        dist.barrier()
+        dist.destroy_process_group()
+        return
+    mode = "samples" if reduce == "peer" else mode
+    sr = D.ShardedRenderer(ep, rank, world, D.TorchCollective(), mode=mode, reduce=reduce)
     for step in range(STEPS):
         lead = None
         if mode == "samples":
@@ -31,7 +41,8 @@ def _worker(rank, world, port, mode, out_dir):
             tiles = m.noise_tiles(SEED, sr.next_frame, FRAMES_PER_RANK)
         used = sr.step(FRAMES_PER_RANK, tiles, lead_in=lead)
         assert used.total_frames == (FRAMES_PER_RANK * world if mode == "samples" else FRAMES_PER_RANK)
-        np.save(os.path.join(out_dir, f"{mode}_{rank}_{step}.npy"), ep.read(sr.output()))
+        np.save(os.path.join(out_dir, f"{mode}{'-peer' if reduce == 'peer' else ''}_{rank}_{step}.npy"), ep.read(sr.output()))
+    sr.close()                                                          # peer mode: let go of the peers' blocks, then a barrier
     dist.barrier()
     dist.destroy_process_group()
 
@@ -42,7 +53,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("mode", ["samples", "rows"])
+@pytest.mark.parametrize("mode", ["samples", "rows", "samples-peer"])
 def test_two_rank_sharding_over_gloo_two_steps(mode, tmp_path):
     import torch.multiprocessing as mp
     world = 2
@@ -50,7 +61,7 @@ def test_two_rank_sharding_over_gloo_two_steps(mode, tmp_path):
     for step in range(STEPS):
         a, b = (np.load(tmp_path / f"{mode}_{k}_{step}.npy") for k in range(world))
         assert np.array_equal(a, b)                                    # every rank holds the combined image
-        frames = (step + 1) * FRAMES_PER_RANK * (world if mode == "samples" else 1)
+        frames = (step + 1) * FRAMES_PER_RANK * (world if mode != "rows" else 1)
         want = sequential_oracle_image(m.Scene.procedural("cornell", 0), W, H, L, SEED, frames)
         if mode == "rows":
             assert np.array_equal(a.view(np.uint32), want.view(np.uint32)), f"step {step}"     # bit-identical
@@ -59,6 +70,14 @@ def test_two_rank_sharding_over_gloo_two_steps(mode, tmp_path):
             rel_rmse = np.sqrt(np.mean((rgb - ref) ** 2)) / max(np.sqrt(np.mean(ref ** 2)), 1e-12)
             assert rel_rmse <= 1e-5, (step, rel_rmse)                  # stated tolerance: fp32 re-association only
             assert (a[..., 3] == 1).all()
+
+
+def test_all_ranks_fail_together_when_one_cannot_map_its_peers(tmp_path):
+    """ShardedRenderer(reduce="peer"): the connect result is exchanged, so no rank is left waiting in a barrier."""
+    import torch.multiprocessing as mp
+    mode = "samples-peer-one-rank-cannot-connect"
+    mp.spawn(_worker, args=(2, _free_port(), mode, str(tmp_path)), nprocs=2, join=True)
+    assert all((tmp_path / f"{mode}_{k}_raised.npy").exists() for k in range(2))
 
 
 def test_frame_plans():
