@@ -262,8 +262,11 @@ int main(int argc, char** argv) {
         else if (!strcmp(a, "--shard")) { o.rows = !strcmp(v, "rows"); if (!o.rows && strcmp(v, "samples")) { fprintf(stderr, "bad --shard\n"); return 2; } ++i; }
         else if (!strcmp(a, "--reduce")) { o.peer = !strcmp(v, "peer"); if (!o.peer && strcmp(v, "nccl")) { fprintf(stderr, "bad --reduce\n"); return 2; } ++i; }
         else if (!strcmp(a, "--pipeline")) {
-            o.pipeline = !strcmp(v, "staged") ? MRT_PIPELINE_STAGED : !strcmp(v, "fused") ? MRT_PIPELINE_MEGAKERNEL
-                       : !strcmp(v, "wavefront") ? MRT_PIPELINE_WAVEFRONT : MRT_PIPELINE_AUTO;
+            if (!strcmp(v, "staged")) o.pipeline = MRT_PIPELINE_STAGED;
+            else if (!strcmp(v, "fused")) o.pipeline = MRT_PIPELINE_MEGAKERNEL;
+            else if (!strcmp(v, "wavefront")) o.pipeline = MRT_PIPELINE_WAVEFRONT;
+            else if (!strcmp(v, "auto")) o.pipeline = MRT_PIPELINE_AUTO;
+            else { fprintf(stderr, "bad --pipeline\n"); return 2; }
             ++i;
         }
         else if (!strcmp(a, "--out")) { o.out = v; ++i; }
