@@ -352,3 +352,62 @@ def test_extension_schedules_agree_on_odd_shapes(c):
             st, oc = r.stats(), o.counts()
             assert (st["primary_rays"], st["shadow_rays"]) == (oc["primary_rays"], oc["shadow_rays"])
     assert_bits(images[0], images[1], "wavefront vs staged")
+
+
+# ---- white furnace: a physical check of the refraction lobe weights (CPU, on the restatement) -------------------------
+def furnace_obj(path, rings=24, segments=48):
+    """A closed box whose walls only emit (Kd 0, Ka 1) around the camera and a glass ball (ior 1.5, smooth normals)."""
+    lines = ["mtllib furnace.mtl"]
+    box = [(-1, 0, -1), (1, 0, -1), (1, 0, 3), (-1, 0, 3), (-1, 2, -1), (1, 2, -1), (1, 2, 3), (-1, 2, 3)]
+    lines += ["v %g %g %g" % p for p in box]
+    lines += ["usemtl wall"] + ["f %d %d %d %d" % q for q in [(1, 4, 3, 2), (5, 6, 7, 8), (1, 2, 6, 5), (2, 3, 7, 6), (3, 4, 8, 7), (4, 1, 5, 8)]]
+    c, rad, first = np.array([0.0, 1.0, 0.0]), 0.5, len(box) + 1
+    for i in range(rings + 1):
+        th = math.pi * i / rings
+        for j in range(segments):
+            ph = 2 * math.pi * j / segments
+            n = np.array([math.sin(th) * math.cos(ph), math.cos(th), math.sin(th) * math.sin(ph)])
+            lines.append("v %.9g %.9g %.9g" % tuple(c + rad * n)); lines.append("vn %.9g %.9g %.9g" % tuple(n))
+    lines.append("usemtl glass")
+    idx = lambda i, j: i * segments + (j % segments)
+    for i in range(rings):
+        for j in range(segments):
+            a, b, cc, d = idx(i, j), idx(i, j + 1), idx(i + 1, j + 1), idx(i + 1, j)
+            for tri in ((a, b, cc), (a, cc, d)):                                   # counter-clockwise seen from outside
+                lines.append("f " + " ".join("%d//%d" % (first + k, k + 1) for k in tri))
+    path.write_text("\n".join(lines) + "\n")
+    path.with_name("furnace.mtl").write_text("newmtl wall\nKd 0 0 0\nKa 1 1 1\nKs 1 0 0\nnewmtl glass\nKd 1 1 1\nKs 0 0 1.5\n")
+
+
+def test_white_furnace_a_glass_ball_is_invisible_with_refraction_and_black_without(tmp_path):
+    """Inside a box whose walls all emit L = 1 (and reflect nothing) every path that reaches a wall carries exactly the
+    product of its lobe weights.  With MRT_EXT_REFRACTION both dielectric lobes weigh 1 and the eta^2 factors telescope
+    to 1 once the path is back in air, so the ball must vanish: its pixels show L = 1.  The reference's branch leaves
+    them black (the continued ray meets the same surface until its bounces are spent) — which is what the extension is for."""
+    furnace_obj(tmp_path / "furnace.obj")
+    scene = m.Scene.load_obj(str(tmp_path / "furnace.obj"))
+    w, h, frames = 64, 48, 8
+    tiles = m.noise_tiles(3, 0, frames)
+    images = {}
+    for flags in (0, m.EXT_REFRACTION):
+        o = orc.Oracle(max_path_length=8)
+        o.init_raytracing(scene); o.drawable_size_will_change(w, h)
+        for s in range(3):
+            o.update_noise(s, m.noise_tile(3, 0xFFFFFFFF))
+        o.set_extensions(flags)
+        o.raygen(0); o.intersect(0)
+        first_hit = o.read_buffer(2)["triangleIndex"].reshape(h, w).copy()
+        o.draw(frames, tiles)
+        images[flags] = o.save_current_image()[..., :3]
+    hit = first_hit >= 12                                        # 12 wall triangles come first (material order)
+    grown, shrunk = hit.copy(), hit.copy()                       # frame 0's primary hits; later frames jitter by up to a pixel,
+    for dy in (-1, 0, 1):                                        # so the silhouette band belongs to neither set
+        for dx in (-1, 0, 1):
+            moved = np.roll(np.roll(hit, dy, axis=0), dx, axis=1)
+            grown |= moved; shrunk &= moved
+    ball, walls = shrunk, ~grown
+    assert 60 < ball.sum() < 1200 and walls.sum() > 2000
+    assert np.allclose(images[0][walls], 1.0, atol=1e-6) and np.allclose(images[m.EXT_REFRACTION][walls], 1.0, atol=1e-6)
+    seen = images[m.EXT_REFRACTION][ball]
+    assert np.allclose(seen, 1.0, atol=1e-5), (seen.min(), seen.max())          # every pixel of the ball shows the wall's radiance
+    assert images[0][ball].mean() < 0.2                          # the reference's straight-through branch: (nearly) black
