@@ -389,12 +389,13 @@ def test_white_furnace_a_glass_ball_is_invisible_with_refraction_and_black_witho
     w, h, frames = 64, 48, 8
     tiles = m.noise_tiles(3, 0, frames)
     images = {}
-    for flags in (0, m.EXT_REFRACTION):
+    DISP = m.EXT_REFRACTION | m.EXT_DISPERSION | m.EXT_CONTINUOUS_SPECTRUM
+    for flags in (0, m.EXT_REFRACTION, DISP):
         o = orc.Oracle(max_path_length=8)
         o.init_raytracing(scene); o.drawable_size_will_change(w, h)
         for s in range(3):
             o.update_noise(s, m.noise_tile(3, 0xFFFFFFFF))
-        o.set_extensions(flags)
+        o.set_extensions(flags, 0.03)
         o.raygen(0); o.intersect(0)
         first_hit = o.read_buffer(2)["triangleIndex"].reshape(h, w).copy()
         o.draw(frames, tiles)
@@ -411,3 +412,6 @@ def test_white_furnace_a_glass_ball_is_invisible_with_refraction_and_black_witho
     seen = images[m.EXT_REFRACTION][ball]
     assert np.allclose(seen, 1.0, atol=1e-5), (seen.min(), seen.max())          # every pixel of the ball shows the wall's radiance
     assert images[0][ball].mean() < 0.2                          # the reference's straight-through branch: (nearly) black
+    # dispersion keeps one channel with weight 3: each sample is (3,0,0), (0,3,0) or (0,0,3), the mean is still the wall's
+    spectral = images[DISP][ball]
+    assert np.allclose(spectral.sum(axis=1), 3.0, atol=1e-4) and np.allclose(spectral.mean(axis=0), 1.0, atol=0.1), spectral.mean(axis=0)
